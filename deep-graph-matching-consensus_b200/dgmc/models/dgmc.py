@@ -1,0 +1,244 @@
+"""DGMC — drop-in for `dgmc.models.DGMC` (reference: dgmc/models/dgmc.py:32-319) whose
+correspondence-and-consensus path runs on hand-written sm_100a kernels (libdgmc_b200).
+
+What stays in Python, on purpose: the module surface (constructor, mutable `num_steps` / `k` /
+`detach` read at call time, parameter names `psi_1.* psi_2.* mlp.0.* mlp.2.*`), the random draws
+(`torch.randint` for negatives, one `torch.randn((B, N_s, R_in))` per consensus step, in the
+reference's order and shapes so a seed reproduces the reference's stream on the same device),
+and the per-node library GEMMs.  Everything index-driven or row-wise is a kernel:
+
+  dgmc.py:85-94    __top_k__            -> K1  ops.topk_*            (scores never hit HBM)
+  dgmc.py:198-201  gather + mul + sum   -> K2  ops.gather_dot
+  dgmc.py:202..225 softmax over k       -> K3  ops.softmax_k / ops.masked_softmax
+  dgmc.py:209-212  scatter_add          -> K4  ops.transport         (by-target CSR gather)
+  dgmc.py:219-223  gather, sub, mlp(D)  -> K6  ops.diff_mlp          (first Linear hoisted)
+  dgmc.py:178-179  dense D and mlp(D)   ->     ops.dense_consensus
+
+There is no CPU path: CPU tensors raise `DgmcNativeError`.
+"""
+import torch
+import torch.nn.functional as F
+from torch.nn import Linear, ReLU, Sequential
+
+from .. import ops
+
+EPS = 1e-8
+
+
+def _pad_batch(x, batch):
+    """[sum N, C] -> ([B, N_max, C] zero-padded, bool mask [B, N_max])  (PyG to_dense_batch as
+    called at dgmc.py:154-155).  batch=None means one graph: a view, no copy."""
+    if batch is None:
+        return x.unsqueeze(0), None
+    num_graphs = int(batch[-1]) + 1
+    sizes = torch.bincount(batch, minlength=num_graphs)
+    n_max = int(sizes.max())
+    first = torch.cumsum(sizes, 0) - sizes
+    slot = batch * n_max + (torch.arange(batch.numel(), device=x.device) - first[batch])
+    dense = x.new_zeros(num_graphs * n_max, x.size(-1))
+    dense[slot] = x
+    mask = torch.zeros(num_graphs * n_max, dtype=torch.bool, device=x.device)
+    mask[slot] = True
+    return dense.view(num_graphs, n_max, -1), mask.view(num_graphs, n_max)
+
+
+def _rows(x, mask):
+    """un-pad: [B, N, R] -> [sum N, R]  (to_sparse, dgmc.py:22-23)."""
+    flat = x.reshape(-1, x.size(-1))
+    return flat if mask is None else flat[mask.view(-1)]
+
+
+def _repad(x, mask):
+    """[sum N, R] -> [B * N_max, R], zeros in the padding (to_dense, dgmc.py:26-29)."""
+    if mask is None:
+        return x
+    out = x.new_zeros(mask.numel(), x.size(-1))
+    out[mask.view(-1)] = x
+    return out
+
+
+class DGMC(torch.nn.Module):
+    r"""Deep Graph Matching Consensus: local matching with :obj:`psi_1`, then :obj:`num_steps`
+    neighbourhood-consensus refinements with :obj:`psi_2`.  Same arguments, attributes, outputs
+    and metrics as the reference class (dgmc.py:64-78); see the module docstring for what runs
+    where.  :obj:`psi_2` must expose :obj:`in_channels` and :obj:`out_channels`."""
+
+    TENSOR_CORE_MIN_PAIRS = 1 << 22  # N_s * N_t below this: the one-warp-per-row exact kernel
+
+    def __init__(self, psi_1, psi_2, num_steps, k=-1, detach=False):
+        super().__init__()
+        self.psi_1, self.psi_2 = psi_1, psi_2
+        self.num_steps, self.k, self.detach = num_steps, k, detach
+        self.backend = 'auto'  # kept for API compatibility (KeOps backend switch, dgmc.py:72)
+        width = psi_2.out_channels
+        self.mlp = Sequential(Linear(width, width), ReLU(), Linear(width, 1))
+
+    def reset_parameters(self):
+        self.psi_1.reset_parameters()
+        self.psi_2.reset_parameters()
+        for layer in self.mlp:
+            if hasattr(layer, 'reset_parameters'):
+                layer.reset_parameters()
+
+    # ---------------------------------------------------------------------------------------
+    def __top_k__(self, x_s, x_t):
+        """[B, N_s, C], [B, N_t, C] -> int64 [B, N_s, k]: per source row the columns of the k
+        largest inner products, descending (dgmc.py:85-94).  The [N_s, N_t] score matrix is never
+        written to memory."""
+        k = self.k
+        if k > x_t.size(1):
+            raise RuntimeError('k=%d exceeds the number of target nodes %d' % (k, x_t.size(1)))
+        x_s, x_t = x_s.detach(), x_t.detach()
+        if ops.topk_tensor_core_ok(x_s, x_t, k) and \
+                x_s.size(1) * x_t.size(1) >= self.TENSOR_CORE_MIN_PAIRS:
+            return ops.topk_tensor_core(x_s, x_t, k).long()
+        return ops.topk_simt(x_s.contiguous(), x_t.contiguous(), k).long()
+
+    def __include_gt__(self, S_idx, s_mask, y):
+        """Make sure y[1] is among the candidates of row y[0]: rows that miss it get their LAST
+        slot overwritten (dgmc.py:96-112).  Like the reference this assumes y[0] ascending."""
+        B, n_s, k = S_idx.shape
+        rows, cols = y[0], y[1]
+        flat = S_idx.reshape(B * n_s, k)
+        if s_mask is not None and not bool(s_mask.all()):
+            real = torch.nonzero(s_mask.view(-1)).view(-1)  # flat real-node index -> padded row
+        else:
+            real = None
+        padded_rows = rows if real is None else real[rows]
+        missing = (flat[padded_rows] != cols.view(-1, 1)).all(dim=-1)
+        flag = torch.zeros(B * n_s, dtype=torch.bool, device=S_idx.device)
+        flag[padded_rows] = missing
+        targets = torch.nonzero(flag).view(-1)  # ascending, as masked_scatter visits them
+        out = flat.clone()
+        out[targets, k - 1] = cols[missing][:targets.numel()]
+        return out.view(B, n_s, k)
+
+    # ---------------------------------------------------------------------------------------
+    def _hoisted_mlp(self):
+        """First consensus-MLP layer as per-node maps, padded to a multiple of 4 channels."""
+        w1, b1 = self.mlp[0].weight, self.mlp[0].bias
+        w2, b2 = self.mlp[2].weight.view(-1), self.mlp[2].bias
+        pad = (-w1.size(0)) % 4
+        if pad:
+            w1, b1, w2 = F.pad(w1, (0, 0, 0, pad)), F.pad(b1, (0, pad)), F.pad(w2, (0, pad))
+        return w1, b1, w2, b2
+
+    def forward(self, x_s, edge_index_s, edge_attr_s, batch_s, x_t, edge_index_t, edge_attr_t,
+                batch_t, y=None):
+        """-> (S_0, S_L): dense [sum N_s, N_t] tensors for k < 1, else un-coalesced sparse COO
+        tensors carrying `.__idx__` [sum N_s, k_eff] int64 and `.__val__` [sum N_s, k_eff]
+        (gradients flow through `__val__`), exactly as dgmc.py:114-244."""
+        h_s = self.psi_1(x_s, edge_index_s, edge_attr_s)
+        h_t = self.psi_1(x_t, edge_index_t, edge_attr_t)
+        if self.detach:
+            h_s, h_t = h_s.detach(), h_t.detach()
+
+        h_s, s_mask = _pad_batch(h_s, batch_s)
+        h_t, t_mask = _pad_batch(h_t, batch_t)
+        assert h_s.size(0) == h_t.size(0), 'Encountered unequal batch-sizes'
+        (B, N_s, C), N_t = h_s.size(), h_t.size(1)
+        R_in = self.psi_2.in_channels
+        w1, b1, w2, b2 = self._hoisted_mlp()
+        num_steps = self.num_steps or 0
+
+        def consensus_nodes(r_s, r_t):
+            """psi_2 on both graphs, then the hoisted first MLP layer -> (P_s, P_t) flat."""
+            o_s = self.psi_2(_rows(r_s, s_mask), edge_index_s, edge_attr_s)
+            o_t = self.psi_2(_rows(r_t, t_mask), edge_index_t, edge_attr_t)
+            o_s, o_t = _repad(o_s, s_mask), _repad(o_t, t_mask)
+            return torch.addmm(b1, o_s, w1.t()), o_t @ w1.t()
+
+        if self.k < 1:
+            # ------ dense variant (dgmc.py:161-183) ------
+            sm = torch.ones(B, N_s, dtype=torch.uint8, device=h_s.device) if s_mask is None \
+                else s_mask.to(torch.uint8)
+            tm = torch.ones(B, N_t, dtype=torch.uint8, device=h_s.device) if t_mask is None \
+                else t_mask.to(torch.uint8)
+            S_hat = h_s @ h_t.transpose(-1, -2)
+            S_0 = _rows(ops.masked_softmax(S_hat, sm, tm), s_mask)
+            for _ in range(num_steps):
+                S = ops.masked_softmax(S_hat, sm, tm)
+                r_s = torch.randn((B, N_s, R_in), dtype=h_s.dtype, device=h_s.device)
+                r_t = S.transpose(-1, -2) @ r_s
+                p_s, p_t = consensus_nodes(r_s, r_t)
+                S_hat = ops.dense_consensus(S_hat, p_s.view(B, N_s, -1), p_t.view(B, N_t, -1), w2,
+                                            b2, sm, tm)
+            S_L = _rows(ops.masked_softmax(S_hat, sm, tm), s_mask)
+            return S_0, S_L
+
+        # ------ sparse variant (dgmc.py:184-244) ------
+        S_idx = self.__top_k__(h_s, h_t)
+        if self.training and y is not None:
+            rnd_size = (B, N_s, min(self.k, N_t - self.k))
+            S_rnd_idx = torch.randint(N_t, rnd_size, dtype=torch.long, device=S_idx.device)
+            S_idx = torch.cat([S_idx, S_rnd_idx], dim=-1)
+            S_idx = self.__include_gt__(S_idx, s_mask, y)
+
+        cand = ops.Candidates(S_idx, N_t)
+        k = cand.k
+        S_hat = ops.gather_dot(h_s.reshape(B * N_s, C), h_t.reshape(B * N_t, C), cand)
+        S_0 = _rows(ops.softmax_k(S_hat), s_mask)
+        for _ in range(num_steps):
+            S = ops.softmax_k(S_hat)
+            r_s = torch.randn((B, N_s, R_in), dtype=h_s.dtype, device=h_s.device)
+            r_t = ops.transport(S, r_s.view(B * N_s, R_in), cand)
+            p_s, p_t = consensus_nodes(r_s, r_t)
+            S_hat = ops.diff_mlp(S_hat, p_s, p_t, w2, b2, cand)
+        S_L = _rows(ops.softmax_k(S_hat), s_mask)
+        S_idx = _rows(S_idx, s_mask)
+
+        # wrap as the reference does (dgmc.py:228-244)
+        n_rows = x_s.size(0)
+        row = torch.arange(n_rows, device=S_idx.device).view(-1, 1).expand(-1, k)
+        coords = torch.stack([row.reshape(-1), S_idx.reshape(-1)], dim=0)
+        size = torch.Size([n_rows, N_t])
+        outs = []
+        for val in (S_0, S_L):
+            sp = torch.sparse_coo_tensor(coords, val.reshape(-1), size,
+                                         requires_grad=val.requires_grad)
+            sp.__idx__, sp.__val__ = S_idx, val
+            outs.append(sp)
+        return outs[0], outs[1]
+
+    # ---------------------------------------------------------------------------------------
+    def loss(self, S, y, reduction='mean'):
+        """Negative log-likelihood of the ground-truth entries (dgmc.py:246-267)."""
+        assert reduction in ['none', 'mean', 'sum']
+        if not S.is_sparse:
+            val = S[y[0], y[1]]
+        else:
+            assert S.__idx__ is not None and S.__val__ is not None
+            hit = S.__idx__[y[0]] == y[1].view(-1, 1)
+            val = S.__val__[y[0]][hit]
+        nll = -torch.log(val + EPS)
+        return nll if reduction == 'none' else getattr(torch, reduction)(nll)
+
+    def acc(self, S, y, reduction='mean'):
+        """Share (or count) of rows y[0] whose arg-max is y[1] (dgmc.py:269-288)."""
+        assert reduction in ['mean', 'sum']
+        if not S.is_sparse:
+            pred = S[y[0]].argmax(dim=-1)
+        else:
+            assert S.__idx__ is not None and S.__val__ is not None
+            pred = S.__idx__[y[0], S.__val__[y[0]].argmax(dim=-1)]
+        correct = (pred == y[1]).sum().item()
+        return correct / y.size(1) if reduction == 'mean' else correct
+
+    def hits_at_k(self, k, S, y, reduction='mean'):
+        """Share (or count) of rows y[0] with y[1] among their k best (dgmc.py:290-311)."""
+        assert reduction in ['mean', 'sum']
+        if not S.is_sparse:
+            pred = S[y[0]].argsort(dim=-1, descending=True)[:, :k]
+        else:
+            assert S.__idx__ is not None and S.__val__ is not None
+            order = S.__val__[y[0]].argsort(dim=-1, descending=True)[:, :k]
+            pred = torch.gather(S.__idx__[y[0]], -1, order)
+        correct = (pred == y[1].view(-1, 1)).sum().item()
+        return correct / y.size(1) if reduction == 'mean' else correct
+
+    def __repr__(self):
+        return ('{}(\n'
+                '    psi_1={},\n'
+                '    psi_2={},\n'
+                '    num_steps={}, k={}\n)').format(type(self).__name__, self.psi_1, self.psi_2,
+                                                    self.num_steps, self.k)

@@ -1,0 +1,438 @@
+"""Host-side wrappers (torch.autograd.Function) around the libdgmc_b200 kernels.
+
+PyTorch provides device memory, the current stream and the autograd tape; every numeric step
+below runs in a hand-written sm_100a kernel reached through the C ABI (`native.call`).  Plain
+per-node GEMMs (`[N, c_in] x [c_in, c_out]`) are left to cuBLAS via torch.matmul in the modules.
+"""
+import torch
+
+from . import native
+from .native import RowStrided, call, query, stream_ptr
+
+
+def _f32(t):
+    if t.dtype != torch.float32:
+        raise native.DgmcNativeError('dgmc (B200): kernels compute in fp32, got %s' % t.dtype)
+    return t.contiguous()
+
+
+def _workspace(nbytes, device):
+    return torch.empty(max(int(nbytes), 1), dtype=torch.uint8, device=device)
+
+
+# --------------------------------------------------------------------------------------------
+# CSR helpers
+# --------------------------------------------------------------------------------------------
+def csr_build(keys, n_seg):
+    """keys int32 [nnz] in [0, n_seg) -> (ptr int32 [n_seg + 1], perm int32 [nnz]), stable."""
+    keys = keys.contiguous()
+    assert keys.dtype == torch.int32
+    nnz = keys.numel()
+    ptr = torch.empty(n_seg + 1, dtype=torch.int32, device=keys.device)
+    perm = torch.empty(nnz, dtype=torch.int32, device=keys.device)
+    ws = _workspace(query('dgmc_csr_build_workspace', nnz, n_seg), keys.device)
+    call('dgmc_csr_build', keys, nnz, n_seg, ptr, perm, ws, ws.numel(), stream_ptr())
+    return ptr, perm
+
+
+def segment_gather(x, out_rows, src, ptr=None, fixed_len=0, src_div=1, w_index=None, w=None,
+                   src_scale=None, seg_scale=None, out=None, accumulate=False):
+    """out[s] = seg_scale[s] * sum_{e in seg(s)} w_e * x[src[e] // src_div]  (see dgmc_b200.h)."""
+    assert x.dim() == 2 and x.stride(1) == 1
+    r = x.size(1)
+    if out is None:
+        out = torch.empty(out_rows, r, dtype=torch.float32, device=x.device)
+        accumulate = False
+    assert out.stride(1) == 1 and out.size(0) == out_rows
+    if out_rows == 0:
+        return out
+    call('dgmc_segment_gather', ptr, int(fixed_len), src, int(src_div), w_index, w, src_scale,
+         seg_scale, RowStrided(x), x.stride(0), RowStrided(out), out.stride(0), out_rows, r,
+         int(bool(accumulate)), stream_ptr())
+    return out
+
+
+class GraphCSR(object):
+    """In-/out-adjacency of one (batched) graph in CSR form, built once per edge_index and cached.
+
+    in_ptr/in_nbr: for node i, the sources j of edges j -> i (PyG flow 'source_to_target',
+    rel.py:27-28); out_ptr/out_nbr: the destinations of edges i -> j ('target_to_source',
+    rel.py:29-30).  inv_in/inv_out = 1 / max(degree, 1) (mean aggregation).  *_edge: the edge
+    id behind each CSR slot (SplineConv needs per-edge data)."""
+    _cache = {}
+
+    def __init__(self, edge_index, num_nodes):
+        src = edge_index[0].to(torch.int32).contiguous()
+        dst = edge_index[1].to(torch.int32).contiguous()
+        self.num_nodes, self.num_edges = num_nodes, src.numel()
+        self.in_ptr, self.in_edge = csr_build(dst, num_nodes)
+        self.out_ptr, self.out_edge = csr_build(src, num_nodes)
+        self.in_nbr = src[self.in_edge.long()].contiguous()
+        self.out_nbr = dst[self.out_edge.long()].contiguous()
+        deg_in = (self.in_ptr[1:] - self.in_ptr[:-1]).clamp_(min=1).to(torch.float32)
+        deg_out = (self.out_ptr[1:] - self.out_ptr[:-1]).clamp_(min=1).to(torch.float32)
+        self.inv_in, self.inv_out = deg_in.reciprocal_(), deg_out.reciprocal_()
+
+    @classmethod
+    def of(cls, edge_index, num_nodes):
+        key = (edge_index.data_ptr(), tuple(edge_index.shape), edge_index._version, num_nodes,
+               str(edge_index.device))
+        hit = cls._cache.get(key)
+        if hit is None or hit[0] is not edge_index:
+            if len(cls._cache) > 64:
+                cls._cache.clear()
+            hit = (edge_index, cls(edge_index, num_nodes))
+            cls._cache[key] = hit
+        return hit[1]
+
+
+class Candidates(object):
+    """The sparse correspondence structure of one forward pass: S_idx (dgmc.py:186-195) as flat
+    int32 target rows plus its by-target CSR (dgmc_csr_build), shared by K2/K4/K6 and their
+    backward kernels.  idx_local: [B, N_s, k] int (graph-local columns)."""
+    def __init__(self, idx_local, n_t):
+        B, n_s, k = idx_local.shape
+        self.B, self.n_s, self.n_t, self.k = B, n_s, n_t, k
+        self.m, self.targets = B * n_s, B * n_t
+        flat = idx_local.to(torch.int32)
+        if B > 1:
+            flat = flat + (torch.arange(B, device=flat.device, dtype=torch.int32) * n_t).view(B, 1, 1)
+        self.idx = flat.reshape(self.m, k).contiguous()
+        self._csr = None
+
+    @property
+    def csr(self):
+        if self._csr is None:
+            self._csr = csr_build(self.idx.view(-1), self.targets)
+        return self._csr
+
+
+# --------------------------------------------------------------------------------------------
+# K3
+# --------------------------------------------------------------------------------------------
+class _SoftmaxK(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        x = _f32(x)
+        y = torch.empty_like(x)
+        call('dgmc_softmax_k_fwd', x, y, x.numel() // x.size(-1), x.size(-1), stream_ptr())
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        y, = ctx.saved_tensors
+        dy = _f32(dy)
+        dx = torch.empty_like(y)
+        call('dgmc_softmax_k_bwd', y, dy, dx, y.numel() // y.size(-1), y.size(-1), stream_ptr())
+        return dx
+
+
+def softmax_k(x):
+    """Row softmax over the last dim (k candidates), dgmc.py:202,205,225."""
+    return _SoftmaxK.apply(x)
+
+
+class _MaskedSoftmax(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, s_mask, t_mask):
+        x = _f32(x)
+        B, n_s, n_t = x.shape
+        y = torch.empty_like(x)
+        call('dgmc_masked_softmax_fwd', x, s_mask, t_mask, y, B, n_s, n_t, stream_ptr())
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        y, = ctx.saved_tensors
+        B, n_s, n_t = y.shape
+        dx = torch.empty_like(y)
+        call('dgmc_masked_softmax_bwd', y, _f32(dy), dx, B, n_s, n_t, stream_ptr())
+        return dx, None, None
+
+
+def masked_softmax(x, s_mask_u8, t_mask_u8):
+    """masked_softmax of dgmc.py:15-19 with S_mask = s_mask (x) t_mask; masks are uint8."""
+    return _MaskedSoftmax.apply(x, s_mask_u8, t_mask_u8)
+
+
+# --------------------------------------------------------------------------------------------
+# K2
+# --------------------------------------------------------------------------------------------
+def _gather_dot_raw(a, b, idx):
+    m, k = idx.shape
+    out = torch.empty(m, k, dtype=torch.float32, device=a.device)
+    call('dgmc_gather_dot_fwd', a, a.stride(0), b, b.stride(0), idx, out, m, k, a.size(1),
+         stream_ptr())
+    return out
+
+
+class _GatherDot(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, a, b, cand):
+        a, b = _f32(a), _f32(b)
+        ctx.cand = cand
+        ctx.save_for_backward(a, b)
+        return _gather_dot_raw(a, b, cand.idx)
+
+    @staticmethod
+    def backward(ctx, g):
+        a, b = ctx.saved_tensors
+        cand, g = ctx.cand, _f32(g)
+        da = db = None
+        if ctx.needs_input_grad[0]:  # da[m] = sum_j g[m,j] b[idx[m,j]]
+            da = segment_gather(b, cand.m, cand.idx.view(-1), fixed_len=cand.k, w=g.view(-1))
+        if ctx.needs_input_grad[1]:  # db[t] = sum_{e -> t} g[e] a[e // k]   (by-target CSR)
+            tptr, perm = cand.csr
+            db = segment_gather(a, cand.targets, perm, ptr=tptr, src_div=cand.k, w_index=perm,
+                                w=g.view(-1))
+        return da, db, None
+
+
+def gather_dot(a, b, cand):
+    """S_hat[m, j] = <a[m], b[idx[m, j]]>  (dgmc.py:198-201).  a [M, C], b [B*N_t, C]."""
+    return _GatherDot.apply(a, b, cand)
+
+
+# --------------------------------------------------------------------------------------------
+# K4
+# --------------------------------------------------------------------------------------------
+class _Transport(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, S, r_s, cand):
+        S, r_s = _f32(S), _f32(r_s)
+        tptr, perm = cand.csr
+        ctx.cand = cand
+        ctx.save_for_backward(S, r_s)
+        return segment_gather(r_s, cand.targets, perm, ptr=tptr, src_div=cand.k, w_index=perm,
+                              w=S.view(-1))
+
+    @staticmethod
+    def backward(ctx, g):
+        S, r_s = ctx.saved_tensors
+        cand, g = ctx.cand, _f32(g)
+        dS = dr = None
+        if ctx.needs_input_grad[0]:  # dS[m, j] = <r_s[m], g[idx[m, j]]>
+            dS = _gather_dot_raw(r_s, g, cand.idx)
+        if ctx.needs_input_grad[1]:  # dr_s[m] = sum_j S[m, j] g[idx[m, j]]
+            dr = segment_gather(g, cand.m, cand.idx.view(-1), fixed_len=cand.k, w=S.view(-1))
+        return dS, dr, None
+
+
+def transport(S, r_s, cand):
+    """r_t[t] = sum_{(m,j): idx[m,j] = t} S[m,j] r_s[m]  (scatter_add at dgmc.py:209-212),
+    computed as a deterministic by-target segmented gather.  -> [B*N_t, R]."""
+    return _Transport.apply(S, r_s, cand)
+
+
+# --------------------------------------------------------------------------------------------
+# K6
+# --------------------------------------------------------------------------------------------
+class _DiffMLP(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, s_hat, ps, pt, w2, b2, cand):
+        s_hat, ps, pt, w2, b2 = _f32(s_hat), _f32(ps), _f32(pt), _f32(w2), _f32(b2)
+        out = torch.empty_like(s_hat)
+        call('dgmc_diff_mlp_fwd', s_hat, ps, pt, cand.idx, w2, b2, out, cand.m, cand.k, ps.size(1),
+             stream_ptr())
+        ctx.cand = cand
+        ctx.save_for_backward(ps, pt, w2)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        ps, pt, w2 = ctx.saved_tensors
+        cand, g = ctx.cand, _f32(g)
+        r = ps.size(1)
+        d_ps = torch.empty_like(ps)
+        d_w2 = torch.empty_like(w2)
+        d_b2 = torch.empty(1, dtype=torch.float32, device=g.device)
+        ws = _workspace(query('dgmc_diff_mlp_bwd_workspace', cand.m, r), g.device)
+        call('dgmc_diff_mlp_bwd_rows', g, ps, pt, cand.idx, w2, d_ps, d_w2, d_b2, cand.m, cand.k, r,
+             ws, ws.numel(), stream_ptr())
+        tptr, perm = cand.csr
+        d_pt = torch.empty_like(pt)
+        call('dgmc_diff_mlp_bwd_targets', g, ps, pt, tptr, perm, w2, d_pt, cand.targets, cand.k, r,
+             stream_ptr())
+        return g, d_ps, d_pt, d_w2, d_b2, None
+
+
+def diff_mlp(s_hat, ps, pt, w2, b2, cand):
+    """S_hat + Lin2(ReLU(Lin1(o_s - o_t[S_idx]))) with Lin1 hoisted to the nodes (dgmc.py:219-223).
+    ps [M, R4], pt [B*N_t, R4] (R4 = R padded to a multiple of 4), w2 [R4], b2 [1]."""
+    return _DiffMLP.apply(s_hat, ps, pt, w2, b2, cand)
+
+
+# --------------------------------------------------------------------------------------------
+# K5: RelConv mean aggregation in both flow directions
+# --------------------------------------------------------------------------------------------
+class _RelAggregate(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, graph):
+        x = _f32(x)
+        n, c = x.shape
+        cat = torch.empty(n, 3 * c, dtype=torch.float32, device=x.device)
+        cat[:, :c] = x
+        segment_gather(x, n, graph.in_nbr, ptr=graph.in_ptr, seg_scale=graph.inv_in,
+                       out=cat[:, c:2 * c])
+        segment_gather(x, n, graph.out_nbr, ptr=graph.out_ptr, seg_scale=graph.inv_out,
+                       out=cat[:, 2 * c:])
+        ctx.graph, ctx.c = graph, c
+        return cat
+
+    @staticmethod
+    def backward(ctx, g):
+        graph, c = ctx.graph, ctx.c
+        g = _f32(g)
+        n = g.size(0)
+        dx = g[:, :c].contiguous()
+        # transpose of mean-in: dx[j] += sum_{e: j -> i} inv_in[i] g_in[i]
+        segment_gather(g[:, c:2 * c], n, graph.out_nbr, ptr=graph.out_ptr, src_scale=graph.inv_in,
+                       out=dx, accumulate=True)
+        # transpose of mean-out: dx[j] += sum_{e: i -> j} inv_out[i] g_out[i]
+        segment_gather(g[:, 2 * c:], n, graph.in_nbr, ptr=graph.in_ptr, src_scale=graph.inv_out,
+                       out=dx, accumulate=True)
+        return dx, None
+
+
+def rel_aggregate(x, graph):
+    """-> [N, 3C] = [x | mean_{j->i} x_j | mean_{i->j} x_j]  (the two propagate calls of
+    rel.py:27-30, taken BEFORE the linear maps: mean(lin(x_j)) == lin(mean(x_j)))."""
+    return _RelAggregate.apply(x, graph)
+
+
+class _NeighborSum(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, graph):
+        ctx.graph = graph
+        x = _f32(x)
+        return segment_gather(x, x.size(0), graph.in_nbr, ptr=graph.in_ptr)
+
+    @staticmethod
+    def backward(ctx, g):
+        graph = ctx.graph
+        g = _f32(g)
+        return segment_gather(g, g.size(0), graph.out_nbr, ptr=graph.out_ptr), None
+
+
+def neighbor_sum(x, graph):
+    """sum_{j -> i} x_j (GINConv's aggregation, gin.py:23 [3p])."""
+    return _NeighborSum.apply(x, graph)
+
+
+# --------------------------------------------------------------------------------------------
+# K5: SplineConv
+# --------------------------------------------------------------------------------------------
+class SplineBasis(object):
+    """(basis, widx) of one edge_attr tensor, computed once and cached (edge attributes are static
+    across the consensus steps and, in the reference scripts, across epochs)."""
+    _cache = {}
+
+    def __init__(self, pseudo, kernel_size):
+        pseudo = _f32(pseudo)
+        if pseudo.dim() == 1:
+            pseudo = pseudo.view(-1, 1)
+        E, dim = pseudo.shape
+        self.n_corners = 1 << dim
+        self.basis = torch.empty(E, self.n_corners, dtype=torch.float32, device=pseudo.device)
+        self.widx = torch.empty(E, self.n_corners, dtype=torch.int32, device=pseudo.device)
+        call('dgmc_spline_basis', pseudo, E, dim, kernel_size, self.basis, self.widx, stream_ptr())
+
+    @classmethod
+    def of(cls, pseudo, kernel_size):
+        key = (pseudo.data_ptr(), tuple(pseudo.shape), pseudo._version, kernel_size,
+               str(pseudo.device))
+        hit = cls._cache.get(key)
+        if hit is None or hit[0] is not pseudo:
+            if len(cls._cache) > 64:
+                cls._cache.clear()
+            hit = (pseudo, cls(pseudo, kernel_size))
+            cls._cache[key] = hit
+        return hit[1]
+
+
+class _SplineGather(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, y, base, graph, sb, n_kernels):
+        """y [N, K*C] -> base + mean-aggregated spline messages [N, C]."""
+        y = _f32(y)
+        n, c = base.shape
+        out = _f32(base).clone()
+        call('dgmc_spline_gather_fwd', y, graph.in_ptr, graph.in_nbr, graph.in_edge, sb.basis,
+             sb.widx, sb.n_corners, graph.inv_in, out, out.stride(0), n, n_kernels, c, 1,
+             stream_ptr())
+        ctx.graph, ctx.sb, ctx.n_kernels = graph, sb, n_kernels
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        graph, sb, K = ctx.graph, ctx.sb, ctx.n_kernels
+        g = _f32(g)
+        n, c = g.shape
+        dy = torch.empty(n, K * c, dtype=torch.float32, device=g.device)
+        call('dgmc_spline_gather_bwd', g, g.stride(0), graph.out_ptr, graph.out_nbr, graph.out_edge,
+             sb.basis, sb.widx, sb.n_corners, graph.inv_in, dy, n, K, c, stream_ptr())
+        return dy, g, None, None, None
+
+
+def spline_gather(y, base, graph, sb, n_kernels):
+    """base[i] + (1/deg_i) sum_{e -> i} sum_s basis[e,s] * y[src_e, widx[e,s]]  (PyG SplineConv)."""
+    return _SplineGather.apply(y, base, graph, sb, n_kernels)
+
+
+# --------------------------------------------------------------------------------------------
+# dense branch
+# --------------------------------------------------------------------------------------------
+class _DenseConsensus(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, s_hat, ps, pt, w2, b2, sm, tm):
+        s_hat, ps, pt, w2, b2 = _f32(s_hat), _f32(ps), _f32(pt), _f32(w2), _f32(b2)
+        B, n_s, n_t = s_hat.shape
+        out = torch.empty_like(s_hat)
+        call('dgmc_dense_consensus_fwd', s_hat, ps, pt, w2, b2, sm, tm, out, B, n_s, n_t,
+             ps.size(-1), stream_ptr())
+        ctx.save_for_backward(ps, pt, w2, sm, tm)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        ps, pt, w2, sm, tm = ctx.saved_tensors
+        g = _f32(g)
+        B, n_s, n_t = g.shape
+        r = ps.size(-1)
+        d_ps, d_pt, d_w2 = torch.empty_like(ps), torch.empty_like(pt), torch.empty_like(w2)
+        d_b2 = torch.empty(1, dtype=torch.float32, device=g.device)
+        ws = _workspace(query('dgmc_dense_consensus_bwd_workspace', r), g.device)
+        call('dgmc_dense_consensus_bwd', g, ps, pt, w2, sm, tm, d_ps, d_pt, d_w2, d_b2, B, n_s, n_t,
+             r, ws, ws.numel(), stream_ptr())
+        return g, d_ps, d_pt, d_w2, d_b2, None, None
+
+
+def dense_consensus(s_hat, ps, pt, w2, b2, sm, tm):
+    """S_hat + mlp(o_s[:, :, None] - o_t[:, None]).masked_fill(~S_mask, 0)  (dgmc.py:178-179)
+    with the first Linear hoisted: ps [B, N_s, R4], pt [B, N_t, R4]."""
+    return _DenseConsensus.apply(s_hat, ps, pt, w2, b2, sm, tm)
+
+
+# --------------------------------------------------------------------------------------------
+# K1
+# --------------------------------------------------------------------------------------------
+def topk_tensor_core_ok(h_s, h_t, k):
+    """Whether the tcgen05 streaming top-k kernel supports this shape."""
+    return False
+
+
+def topk_tensor_core(h_s, h_t, k):
+    raise native.DgmcNativeError('tensor-core top-k not built')
+
+
+def topk_simt(h_s, h_t, k, want_scores=False):
+    """Exact fp32 top-k for small pairs: h_s [B, N_s, C], h_t [B, N_t, C] -> int32 [B, N_s, k]."""
+    h_s, h_t = _f32(h_s), _f32(h_t)
+    B, n_s, c = h_s.shape
+    n_t = h_t.size(1)
+    idx = torch.empty(B, n_s, k, dtype=torch.int32, device=h_s.device)
+    score = torch.empty(B, n_s, k, dtype=torch.float32, device=h_s.device) if want_scores else None
+    call('dgmc_topk_simt', h_s, h_t, B, n_s, n_t, c, k, idx, score, stream_ptr())
+    return (idx, score) if want_scores else idx

@@ -1,0 +1,149 @@
+/* libdgmc_b200 — C ABI of the B200 (sm_100a) kernels behind `dgmc.models.DGMC`.
+ *
+ * This is the drop-in boundary for the reference's correspondence-and-consensus path
+ * (/root/reference/dgmc/models/dgmc.py:114-311 and the psi backbones rel.py / spline.py).
+ * The reference has no native code of its own: every entry point below replaces a
+ * THIRD-PARTY native routine the reference reaches from Python (ATen, torch_scatter,
+ * torch_spline_conv, KeOps); the comment on each one cites the reference call site.
+ *
+ * Conventions
+ *  - all pointers are DEVICE pointers on the current device unless marked "host";
+ *  - values are fp32, indices int32 (the Python host converts int64 at the boundary),
+ *    masks are uint8 (0/1); matrices are row-major, `ld*` = row stride in elements;
+ *  - every call is asynchronous on `stream` (a cudaStream_t), performs no hidden sync and
+ *    NEVER allocates or frees: outputs and workspaces belong to the caller
+ *    (`*_workspace()` returns the bytes a call needs);
+ *  - return value 0 on success, negative on failure (DGMC_ERR_*); `dgmc_last_error()`
+ *    returns a thread-local description.  No exceptions cross the boundary.
+ */
+#ifndef DGMC_B200_H
+#define DGMC_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DGMC_B200_ABI_VERSION 1
+
+typedef struct CUstream_st* dgmc_stream_t; /* == cudaStream_t */
+
+const char* dgmc_last_error(void);
+int dgmc_abi_version(void);
+
+/* ---- K1 (small shapes): exact fp32 top-k, one warp per source row ------------------------
+ * idx_out[b, i, 0:k] = columns j of the k largest <h_s[b,i,:], h_t[b,j,:]>, descending, ties by
+ * ascending j (graph-local column ids); score_out (nullable) the fp32 scores.
+ * replaces DGMC.__top_k__ (dgmc.py:85-94: KeOps argKmin, else broadcast-mul-sum + topk) when
+ * the pair is too small for a tensor-core tile.  h_s [B, n_s, c], h_t [B, n_t, c] contiguous. */
+int dgmc_topk_simt(const float* h_s, const float* h_t, int B, int n_s, int n_t, int c, int k,
+                   int32_t* idx_out, float* score_out, dgmc_stream_t stream);
+
+/* ---- K3: row softmax over the k candidates -------------------------------------------
+ * replaces ATen softmax at dgmc.py:202,205,225 (sparse branch: un-masked). */
+int dgmc_softmax_k_fwd(const float* x, float* y, int64_t rows, int k, dgmc_stream_t stream);
+int dgmc_softmax_k_bwd(const float* y, const float* dy, float* dx, int64_t rows, int k,
+                       dgmc_stream_t stream);
+
+/* ---- K3 (dense branch): masked row softmax -------------------------------------------
+ * replaces masked_fill + softmax + masked_fill, dgmc.py:15-19 as used at :165,168,181.
+ * x,y: [B, n_s, n_t]; s_mask [B, n_s], t_mask [B, n_t].  Entries outside
+ * s_mask (x) t_mask come out as exactly 0 (the reference's NaN rows are re-zeroed too). */
+int dgmc_masked_softmax_fwd(const float* x, const uint8_t* s_mask, const uint8_t* t_mask, float* y,
+                            int B, int n_s, int n_t, dgmc_stream_t stream);
+int dgmc_masked_softmax_bwd(const float* y, const float* dy, float* dx, int B, int n_s, int n_t,
+                            dgmc_stream_t stream);
+
+/* ---- K2: candidate gather-dot ---------------------------------------------------------
+ * out[m, j] = < a[m, :], b[idx[m, j], :] >.  replaces gather + mul + sum at dgmc.py:198-201
+ * (S_hat initialisation) and is the backward of the indicator transport (dS = <r_s, dr_t>).
+ * idx holds FLAT row numbers of b (graph offset already added). */
+int dgmc_gather_dot_fwd(const float* a, int64_t lda, const float* b, int64_t ldb,
+                        const int32_t* idx, float* out, int64_t m, int k, int c,
+                        dgmc_stream_t stream);
+
+/* ---- CSR construction: stable counting (radix) sort of `keys` --------------------------
+ * ptr[s] .. ptr[s+1] delimit, in `perm`, the positions e (ascending) with keys[e] == s.
+ * Used for (i) the by-target view of the candidate lists S_idx, rebuilt once per forward,
+ * which turns torch_scatter.scatter_add (dgmc.py:209-212) into a deterministic segmented
+ * gather, and (ii) the in-/out-adjacency of each graph (PyG propagate, rel.py:28,30), built
+ * once per edge_index and cached by the host. */
+size_t dgmc_csr_build_workspace(int64_t nnz, int64_t n_seg);
+int dgmc_csr_build(const int32_t* keys, int64_t nnz, int64_t n_seg, int32_t* ptr, int32_t* perm,
+                   void* workspace, size_t workspace_bytes, dgmc_stream_t stream);
+
+/* ---- K4 / K5: segmented weighted gather-reduce -----------------------------------------
+ * out[s, 0:r] = seg_scale[s] * sum_{e in seg(s)} w_e * X[row_e, 0:r]
+ *   seg(s)  = [ptr[s], ptr[s+1])            if ptr != NULL, else [s*fixed_len, (s+1)*fixed_len)
+ *   row_e   = src[e] / src_div              (src_div >= 1; lets `perm` of entry ids m*k+j address row m)
+ *   w_e     = (w ? w[w_index ? w_index[e] : e] : 1) * (src_scale ? src_scale[row_e] : 1)
+ *   seg_scale may be NULL (= 1).  accumulate != 0 adds into `out` instead of overwriting it.
+ * replaces: scatter_add of r_s (x) S (dgmc.py:209-212) as a by-target gather [K4]; its
+ * backward dr_s; PyG mean aggregation x_j -> i in both flow directions (rel.py:27-30) and the
+ * transposed aggregation of their backward [K5]; the scatter_add_ backward of the gathers at
+ * dgmc.py:200,221. */
+int dgmc_segment_gather(const int32_t* ptr, int fixed_len, const int32_t* src, int src_div,
+                        const int32_t* w_index, const float* w, const float* src_scale,
+                        const float* seg_scale, const float* x, int64_t ldx, float* out,
+                        int64_t ldo, int64_t n_seg, int r, int accumulate, dgmc_stream_t stream);
+
+/* ---- K6: difference gather + consensus MLP update (hoisted first layer) -----------------
+ * s_out[m, j] = s_in[m, j] + b2 + sum_c w2[c] * relu(ps[m, c] - pt[idx[m, j], c])
+ * with ps = o_s W1^T + b1 and pt = o_t W1^T computed per NODE by the host (library GEMM):
+ * Lin1(o_s - o_t) = W1 o_s - W1 o_t + b1.  replaces gather, sub and mlp(D) at dgmc.py:219-223
+ * without materialising D [B, N_s, k, R].  b2 is a device pointer to one float. */
+int dgmc_diff_mlp_fwd(const float* s_in, const float* ps, const float* pt, const int32_t* idx,
+                      const float* w2, const float* b2, float* s_out, int64_t m, int k, int r,
+                      dgmc_stream_t stream);
+/* backward, row side: d_ps[m, c] = w2[c] * sum_j g[m, j] * [ps[m,c] > pt[idx[m,j],c]];
+ * d_w2[c] = sum_{m,j} g[m,j] * relu(...); d_b2 = sum g.  Two-stage deterministic reduction
+ * through `workspace`. */
+size_t dgmc_diff_mlp_bwd_workspace(int64_t m, int r);
+int dgmc_diff_mlp_bwd_rows(const float* g, const float* ps, const float* pt, const int32_t* idx,
+                           const float* w2, float* d_ps, float* d_w2, float* d_b2, int64_t m,
+                           int k, int r, void* workspace, size_t workspace_bytes,
+                           dgmc_stream_t stream);
+/* backward, target side (by-target CSR of idx: tptr/perm from dgmc_csr_build):
+ * d_pt[t, c] = -w2[c] * sum_{e in seg(t)} g[perm[e]] * [ps[perm[e]/k, c] > pt[t, c]]. */
+int dgmc_diff_mlp_bwd_targets(const float* g, const float* ps, const float* pt,
+                              const int32_t* tptr, const int32_t* perm, const float* w2,
+                              float* d_pt, int64_t n_t, int k, int r, dgmc_stream_t stream);
+
+/* ---- K5 (SplineConv): degree-1 open B-spline convolution -----------------------------------
+ * replaces torch_spline_conv's spline_basis / spline_weighting and the scatter-mean of PyG
+ * SplineConv(kernel_size=5) as constructed at spline.py:21 ([3p]; forward used at spline.py:49).
+ * basis/widx: [n_edges, 2^dim]; pseudo in [0, 1]^dim.  The host computes
+ * Y[n, kk, :] = x[n] @ W[kk] with one library GEMM; gather_fwd reduces it along the in-edges
+ * (CSR by destination: in_ptr / in_nbr = source node / in_edge = edge id), gather_bwd produces
+ * dY along the out-edges (CSR by source).  inv_deg = 1 / max(in-degree, 1).  Gradients with
+ * respect to pseudo are not provided (edge attributes are data in every reference script). */
+int dgmc_spline_basis(const float* pseudo, int64_t n_edges, int dim, int kernel_size, float* basis,
+                      int32_t* widx, dgmc_stream_t stream);
+int dgmc_spline_gather_fwd(const float* y, const int32_t* in_ptr, const int32_t* in_nbr,
+                           const int32_t* in_edge, const float* basis, const int32_t* widx,
+                           int n_corners, const float* inv_deg, float* out, int64_t ldo, int64_t n,
+                           int n_kernels, int c, int accumulate, dgmc_stream_t stream);
+int dgmc_spline_gather_bwd(const float* g, int64_t ldg, const int32_t* out_ptr,
+                           const int32_t* out_nbr, const int32_t* out_edge, const float* basis,
+                           const int32_t* widx, int n_corners, const float* inv_deg, float* dy,
+                           int64_t n, int n_kernels, int c, dgmc_stream_t stream);
+
+/* ---- dense branch: consensus update without materialising D [B, N_s, N_t, R] ----------------
+ * s_out[b,i,j] = s_in[b,i,j] + [s_mask[b,i] & t_mask[b,j]] * (b2 + sum_c w2[c] relu(ps[b,i,c] - pt[b,j,c]))
+ * replaces D = o_s[:, :, None] - o_t[:, None], mlp(D).masked_fill(~S_mask, 0) at dgmc.py:178-179
+ * (first Linear hoisted to the nodes as in K6).  ps [B, n_s, r], pt [B, n_t, r]. */
+int dgmc_dense_consensus_fwd(const float* s_in, const float* ps, const float* pt, const float* w2,
+                             const float* b2, const uint8_t* s_mask, const uint8_t* t_mask,
+                             float* s_out, int B, int n_s, int n_t, int r, dgmc_stream_t stream);
+size_t dgmc_dense_consensus_bwd_workspace(int r);
+int dgmc_dense_consensus_bwd(const float* g, const float* ps, const float* pt, const float* w2,
+                             const uint8_t* s_mask, const uint8_t* t_mask, float* d_ps, float* d_pt,
+                             float* d_w2, float* d_b2, int B, int n_s, int n_t, int r,
+                             void* workspace, size_t workspace_bytes, dgmc_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DGMC_B200_H */

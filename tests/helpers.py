@@ -69,3 +69,97 @@ def assert_parity(new, ref64, ref32, rel=1e-5, floor=1e-7, what=''):
     worst = (err - bound).max().item()
     assert worst <= 0, '%s: exceeds parity bound by %.3g (max err %.3g)' % (what, worst,
                                                                         err.max().item())
+
+
+# ---------------------------------------------------------------------------------------------
+# product side (CUDA path through the C ABI)
+# ---------------------------------------------------------------------------------------------
+import contextlib  # noqa: E402
+
+
+@contextlib.contextmanager
+def replay_draws(draws, device):
+    """Make torch.randn / torch.randint return the draws the reference made (RNG contract,
+    SURVEY.md §8b): the product calls them with the reference's shapes and order."""
+    real_randn, real_randint = torch.randn, torch.randint
+    state = {'i': 0}
+
+    def randn(size, *a, dtype=None, device=None, **kw):
+        t = draws['r_s'][state['i']]
+        state['i'] += 1
+        assert tuple(t.shape) == tuple(size), (t.shape, size)
+        return t.to(device=device, dtype=dtype or torch.float32)
+
+    def randint(high, size, *a, dtype=None, device=None, **kw):
+        t = draws['neg']
+        assert t is not None and tuple(t.shape) == tuple(size), (None if t is None else t.shape, size)
+        return t.to(device=device)
+
+    torch.randn, torch.randint = randn, randint
+    try:
+        yield
+    finally:
+        torch.randn, torch.randint = real_randn, real_randint
+
+
+def build_product_psi(spec):
+    from dgmc.models import GIN, RelCNN, SplineCNN
+    if spec['kind'] == 'rel':
+        return RelCNN(spec['in'], spec['out'], spec['layers'], batch_norm=spec.get('batch_norm', False),
+                      cat=spec.get('cat', True), lin=spec.get('lin', True),
+                      dropout=spec.get('dropout', 0.0))
+    if spec['kind'] == 'spline':
+        return SplineCNN(spec['in'], spec['out'], spec['dim'], spec['layers'],
+                         cat=spec.get('cat', True), lin=spec.get('lin', True),
+                         dropout=spec.get('dropout', 0.0))
+    if spec['kind'] == 'gin':
+        return GIN(spec['in'], spec['out'], spec['layers'], batch_norm=spec.get('batch_norm', False),
+                   cat=spec.get('cat', True), lin=spec.get('lin', True))
+    raise ValueError(spec['kind'])
+
+
+def build_product(case, device):
+    from dgmc.models import DGMC
+    model = DGMC(build_product_psi(case['spec1']), build_product_psi(case['spec2']),
+                 num_steps=case['num_steps'], k=case['k'], detach=case['detach'])
+    missing, unexpected = model.load_state_dict(case['params'], strict=False)
+    assert not unexpected, unexpected
+    assert all('num_batches_tracked' in m or 'running_' in m for m in missing), missing
+    return model.to(device)
+
+
+def run_product(case, device='cuda'):
+    """Product forward (+ loss + backward) on a golden case, draws replayed."""
+    model = build_product(case, device)
+    model.train(case['training'])
+    model.zero_grad()
+    inp = {k: (v.to(device) if torch.is_tensor(v) else v) for k, v in case['inputs'].items()}
+    y = case['y'].to(device) if case['y'] is not None else None
+    args = [inp[n] for n in ('x_s', 'edge_index_s', 'edge_attr_s', 'batch_s', 'x_t', 'edge_index_t',
+                             'edge_attr_t', 'batch_t')]
+    with replay_draws(case['draws'], device):
+        if y is not None and case['training'] and case['k'] >= 1:
+            S_0, S_L = model(*args, y)
+        else:
+            S_0, S_L = model(*args)
+    res = {'model': model}
+    if S_0.is_sparse:
+        res['idx'], res['S_0'], res['S_L'] = S_0.__idx__, S_0.__val__, S_L.__val__
+        res['S_0_sparse'], res['S_L_sparse'] = S_0, S_L
+    else:
+        res['S_0'], res['S_L'] = S_0, S_L
+    if y is not None:
+        res['loss_0'], res['loss_L'] = model.loss(S_0, y), model.loss(S_L, y)
+        res['acc_L'], res['hits3_L'] = model.acc(S_L, y), model.hits_at_k(3, S_L, y)
+        if case['training']:
+            total = {'0': res['loss_0'], 'L': res['loss_L'],
+                     '0+L': res['loss_0'] + res['loss_L']}[case['loss_on']]
+            total.backward()
+            res['grads'] = {n: p.grad for n, p in model.named_parameters() if p.grad is not None}
+    return res
+
+
+def sort_rows_by_index(idx, *vals):
+    """Candidate order inside a row is not part of the contract."""
+    order = idx.argsort(dim=-1, stable=True)
+    return (torch.gather(idx, -1, order), ) + tuple(torch.gather(v, -1, order) for v in vals)

@@ -1,0 +1,90 @@
+"""End-to-end parity of the CUDA path (through the public API and the C ABI) against the golden
+vectors recorded from the unmodified reference.  Tolerance (SURVEY.md §8c / BASELINE.json):
+|new - ref64| <= max(1e-5 |ref64|, 2 |ref32 - ref64|) + 1e-7 for S_0 / S_L / loss; candidate index
+sets bit-exact; gradients within 1e-4 of the largest gradient entry (fp32 noise of the reference
+itself is 5e-5 of max)."""
+import pytest
+import torch
+
+from helpers import (assert_parity, golden_names, load_case, run_product, sort_rows_by_index)
+
+pytestmark = pytest.mark.gpu
+
+NAMES = golden_names()
+
+
+@pytest.mark.parametrize('name', NAMES)
+def test_golden_case(name):
+    case = load_case(name)
+    ref64, ref32 = case['out64'], case['out32']
+    got = run_product(case)
+    if 'idx' in ref64:
+        gi, g0, gL = sort_rows_by_index(got['idx'].cpu(), got['S_0'].detach().cpu(),
+                                        got['S_L'].detach().cpu())
+        ri, r0, rL = sort_rows_by_index(ref64['idx'], ref64['S_0'], ref64['S_L'])
+        _, q0, qL = sort_rows_by_index(ref32['idx'], ref32['S_0'], ref32['S_L'])
+        assert torch.equal(gi, ri), 'candidate index sets differ'
+        assert_parity(g0, r0, q0, what='S_0')
+        assert_parity(gL, rL, qL, what='S_L')
+    else:
+        assert_parity(got['S_0'], ref64['S_0'], ref32['S_0'], what='S_0')
+        assert_parity(got['S_L'], ref64['S_L'], ref32['S_L'], what='S_L')
+    if 'loss_L' in ref64:
+        assert_parity(got['loss_0'], ref64['loss_0'], ref32['loss_0'], what='loss_0')
+        assert_parity(got['loss_L'], ref64['loss_L'], ref32['loss_L'], what='loss_L')
+        assert got['acc_L'] == pytest.approx(ref64['acc_L'].item())
+        assert got['hits3_L'] == pytest.approx(ref64['hits3_L'].item())
+    if 'grads' in ref64:
+        assert set(got['grads']) == set(ref64['grads'])
+        for k, g in ref64['grads'].items():
+            scale = g.abs().max().item()
+            err = (got['grads'][k].double().cpu() - g).abs().max().item()
+            noise = (ref32['grads'][k].double() - g).abs().max().item()
+            assert err <= max(1e-4 * scale, 3 * noise) + 1e-9, \
+                'grad %s: err %.3g, scale %.3g, ref fp32 noise %.3g' % (k, err, scale, noise)
+
+
+def test_sparse_output_contract():
+    case = load_case('gin_batched_sparse_kN')
+    got = run_product(case)
+    S = got['S_L_sparse']
+    assert S.is_sparse and S.size() == (8, 4)
+    assert S.__idx__.dtype == torch.int64 and S.__idx__.shape == (8, 4)
+    dense = S.to_dense()
+    assert torch.allclose(dense.cpu().double(), case['out64']['S_L_dense'], atol=1e-5)
+    assert torch.allclose(dense.sum(-1), torch.ones(8, device=dense.device), atol=1e-5)
+
+
+def test_dense_equals_sparse_k_equals_n():
+    # the reference's own invariant, test/models/test_dgmc.py:29-64
+    dense, sparse = load_case('gin_batched_dense'), load_case('gin_batched_sparse_kN')
+    sparse['params'] = dense['params']
+    sparse['draws'] = {'r_s': dense['draws']['r_s'], 'neg': None}
+    sparse['training'] = False
+    dense['training'] = False
+    a, b = run_product(dense), run_product(sparse)
+    assert torch.allclose(a['S_0'], b['S_0_sparse'].to_dense(), atol=1e-6)
+    assert torch.allclose(a['S_L'], b['S_L_sparse'].to_dense(), atol=1e-6)
+    assert torch.allclose(a['loss_0'], b['loss_0'], atol=1e-6)
+    assert a['acc_L'] == b['acc_L']
+
+
+def test_include_gt_known_answer():
+    # test/models/test_dgmc.py:87-95
+    from dgmc.models import DGMC, GIN
+    model = DGMC(GIN(32, 16, 2), GIN(8, 8, 2), num_steps=1)
+    S_idx = torch.tensor([[[0, 1], [1, 2]], [[1, 2], [0, 1]]]).cuda()
+    s_mask = torch.tensor([[True, False], [True, True]]).cuda()
+    y = torch.tensor([[0, 1], [0, 0]]).cuda()
+    out = model.__include_gt__(S_idx, s_mask, y)
+    assert out.tolist() == [[[0, 1], [1, 2]], [[1, 0], [0, 1]]]
+
+
+def test_cpu_tensors_fail_loudly():
+    from dgmc import native
+    from dgmc.models import DGMC, RelCNN
+    model = DGMC(RelCNN(8, 8, 1), RelCNN(4, 4, 1), num_steps=1, k=2)
+    x = torch.randn(5, 8)
+    e = torch.tensor([[0, 1, 2], [1, 2, 3]])
+    with pytest.raises(native.DgmcNativeError):
+        model(x, e, None, None, x, e, None, None)

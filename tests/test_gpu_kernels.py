@@ -1,0 +1,277 @@
+"""Per-kernel parity: each C-ABI entry point against a plain PyTorch restatement of the reference
+op it replaces, on seeded inputs (fp32; tolerances written at each assert; index outputs
+bit-exact).  Runs on the GPU box only."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+DEV = 'cuda'
+
+
+def _gen(seed):
+    return torch.Generator(device='cpu').manual_seed(seed)
+
+
+def _randn(g, *shape):
+    return torch.randn(*shape, generator=g).to(DEV)
+
+
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize('rows,k', [(1, 1), (7, 5), (1000, 20), (333, 50), (64, 130)])
+def test_softmax_k(rows, k):
+    from dgmc import ops
+    g = _gen(rows + k)
+    x = (_randn(g, rows, k) * 3).requires_grad_()
+    dy = _randn(g, rows, k)
+    y = ops.softmax_k(x)
+    y.backward(dy)
+    xr = x.detach().double().requires_grad_()
+    yr = xr.softmax(-1)
+    yr.backward(dy.double())
+    assert torch.allclose(y.double(), yr, rtol=1e-5, atol=1e-7)
+    assert torch.allclose(x.grad.double(), xr.grad, rtol=1e-4, atol=1e-7)
+
+
+def test_masked_softmax_ragged():
+    from dgmc import ops
+    g = _gen(3)
+    B, ns, nt = 5, 9, 37
+    x = _randn(g, B, ns, nt).requires_grad_()
+    sm = (torch.rand(B, ns, generator=g) > 0.3).to(DEV)
+    tm = (torch.rand(B, nt, generator=g) > 0.3).to(DEV)
+    tm[:, 0] = True
+    y = ops.masked_softmax(x, sm.to(torch.uint8), tm.to(torch.uint8))
+    dy = _randn(g, B, ns, nt)
+    y.backward(dy)
+    mask = sm.unsqueeze(2) & tm.unsqueeze(1)
+    xr = x.detach().double().requires_grad_()
+    yr = xr.masked_fill(~mask, float('-inf')).softmax(-1).masked_fill(~mask, 0)  # dgmc.py:15-19
+    yr = torch.nan_to_num(yr, nan=0.0)
+    keep = sm.unsqueeze(2).expand_as(yr)
+    (yr * keep).backward(dy.double())
+    assert torch.allclose(y.double(), yr * keep, rtol=1e-5, atol=1e-7)
+    assert torch.allclose(x.grad.double(), torch.nan_to_num(xr.grad), rtol=1e-4, atol=1e-7)
+
+
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize('nnz,n_seg', [(0, 5), (1, 1), (1000, 7), (5000, 300), (70000, 19572),
+                                       (200000, 1 << 17)])
+def test_csr_build_is_a_stable_sort(nnz, n_seg):
+    from dgmc import ops
+    g = _gen(nnz + n_seg)
+    keys = torch.randint(n_seg, (nnz, ), generator=g, dtype=torch.int32).to(DEV)
+    if nnz > 100:  # a hub segment
+        keys[::3] = n_seg // 2
+    ptr, perm = ops.csr_build(keys, n_seg)
+    order = torch.sort(keys.long(), stable=True)[1]
+    assert torch.equal(perm.long(), order)
+    counts = torch.bincount(keys.long(), minlength=n_seg)
+    expect = torch.cat([torch.zeros(1, dtype=torch.long, device=DEV), counts.cumsum(0)])
+    assert torch.equal(ptr.long(), expect)
+
+
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize('c', [8, 32, 64, 100, 128, 256, 300, 384, 512, 7])
+def test_gather_dot_and_backward(c):
+    from dgmc import ops
+    g = _gen(c)
+    m, nt, k = 200, 150, 12
+    a = _randn(g, m, c).requires_grad_()
+    b = _randn(g, nt, c).requires_grad_()
+    idx = torch.randint(nt, (1, m, k), generator=g).to(DEV)
+    cand = ops.Candidates(idx, nt)
+    out = ops.gather_dot(a, b, cand)
+    go = _randn(g, m, k)
+    out.backward(go)
+    ar, br = a.detach().double().requires_grad_(), b.detach().double().requires_grad_()
+    ref = (ar.unsqueeze(1) * br[idx[0]]).sum(-1)  # dgmc.py:198-201
+    ref.backward(go.double())
+    assert torch.allclose(out.double(), ref, rtol=1e-5, atol=1e-5)
+    assert torch.allclose(a.grad.double(), ar.grad, rtol=1e-5, atol=1e-5)
+    assert torch.allclose(b.grad.double(), br.grad, rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.parametrize('B,r', [(1, 32), (1, 64), (3, 8), (2, 128), (1, 6)])
+def test_transport_matches_scatter_add(B, r):
+    from dgmc import ops
+    g = _gen(B * 100 + r)
+    ns, nt, k = 90, 70, 9
+    S = torch.rand(B * ns, k, generator=g).to(DEV).requires_grad_()
+    r_s = _randn(g, B * ns, r).requires_grad_()
+    idx = torch.randint(nt, (B, ns, k), generator=g).to(DEV)
+    cand = ops.Candidates(idx, nt)
+    r_t = ops.transport(S, r_s, cand)
+    go = _randn(g, B * nt, r)
+    r_t.backward(go)
+    Sr, rr = S.detach().double().requires_grad_(), r_s.detach().double().requires_grad_()
+    contrib = (rr.view(B, ns, 1, r) * Sr.view(B, ns, k, 1)).reshape(B, ns * k, r)
+    ref = torch.zeros(B, nt, r, dtype=torch.double, device=DEV)
+    ref = ref.scatter_add(1, idx.view(B, ns * k, 1).expand(-1, -1, r), contrib)  # dgmc.py:209-212
+    ref.view(B * nt, r).backward(go.double())
+    assert torch.allclose(r_t.double(), ref.view(B * nt, r), rtol=1e-5, atol=1e-6)
+    assert torch.allclose(S.grad.double(), Sr.grad, rtol=1e-5, atol=1e-5)
+    assert torch.allclose(r_s.grad.double(), rr.grad, rtol=1e-5, atol=1e-5)
+    # determinism: by-target CSR order is fixed
+    assert torch.equal(ops.transport(S, r_s, ops.Candidates(idx, nt)), r_t)
+
+
+@pytest.mark.parametrize('B,r', [(1, 64), (1, 32), (2, 8), (1, 128), (1, 256)])
+def test_diff_mlp_matches_reference_mlp(B, r):
+    from dgmc import ops
+    g = _gen(B + r)
+    ns, nt, k = 80, 60, 11
+    lin1 = torch.nn.Linear(r, r).to(DEV)
+    lin2 = torch.nn.Linear(r, 1).to(DEV)
+    o_s = _randn(g, B * ns, r).requires_grad_()
+    o_t = _randn(g, B * nt, r).requires_grad_()
+    s_hat = _randn(g, B * ns, k).requires_grad_()
+    idx = torch.randint(nt, (B, ns, k), generator=g).to(DEV)
+    cand = ops.Candidates(idx, nt)
+    ps = torch.addmm(lin1.bias, o_s, lin1.weight.t())
+    pt = o_t @ lin1.weight.t()
+    out = ops.diff_mlp(s_hat, ps, pt, lin2.weight.view(-1), lin2.bias, cand)
+    go = _randn(g, B * ns, k)
+    out.backward(go)
+    got = [t.grad.clone() for t in (s_hat, o_s, o_t, lin1.weight, lin1.bias, lin2.weight, lin2.bias)]
+    # reference formulation, dgmc.py:219-223, in fp64
+    d = lambda t: t.detach().double().requires_grad_()  # noqa: E731
+    s2, os2, ot2 = d(s_hat), d(o_s), d(o_t)
+    w1, b1, w2, b2 = d(lin1.weight), d(lin1.bias), d(lin2.weight), d(lin2.bias)
+    D = os2.view(B, ns, 1, r) - ot2.view(B, nt, r)[torch.arange(B, device=DEV).view(B, 1, 1), idx]
+    hid = torch.relu(D @ w1.t() + b1)
+    ref = s2 + (hid @ w2.t() + b2).squeeze(-1).view(B * ns, k)
+    ref.backward(go.double())
+    assert torch.allclose(out.double(), ref, rtol=1e-5, atol=2e-5)
+    for a, b_ in zip(got, (s2, os2, ot2, w1, b1, w2, b2)):
+        scale = b_.grad.abs().max().item() + 1e-12
+        assert (a.double() - b_.grad).abs().max().item() <= 2e-5 * scale + 1e-6
+
+
+def test_dense_consensus_matches_reference_mlp():
+    from dgmc import ops
+    g = _gen(11)
+    B, ns, nt, r = 4, 13, 17, 16
+    lin1 = torch.nn.Linear(r, r).to(DEV)
+    lin2 = torch.nn.Linear(r, 1).to(DEV)
+    o_s = _randn(g, B, ns, r).requires_grad_()
+    o_t = _randn(g, B, nt, r).requires_grad_()
+    s_hat = _randn(g, B, ns, nt).requires_grad_()
+    sm = (torch.rand(B, ns, generator=g) > 0.2).to(DEV)
+    tm = (torch.rand(B, nt, generator=g) > 0.2).to(DEV)
+    ps = o_s @ lin1.weight.t() + lin1.bias
+    pt = o_t @ lin1.weight.t()
+    out = ops.dense_consensus(s_hat, ps, pt, lin2.weight.view(-1), lin2.bias, sm.to(torch.uint8),
+                              tm.to(torch.uint8))
+    go = _randn(g, B, ns, nt)
+    out.backward(go)
+    got = [t.grad.clone() for t in (s_hat, o_s, o_t, lin1.weight, lin1.bias, lin2.weight, lin2.bias)]
+    d = lambda t: t.detach().double().requires_grad_()  # noqa: E731
+    s2, os2, ot2 = d(s_hat), d(o_s), d(o_t)
+    w1, b1, w2, b2 = d(lin1.weight), d(lin1.bias), d(lin2.weight), d(lin2.bias)
+    mask = sm.unsqueeze(2) & tm.unsqueeze(1)
+    D = os2.unsqueeze(2) - os2.new_zeros(1) - ot2.unsqueeze(1)
+    upd = (torch.relu(D @ w1.t() + b1) @ w2.t() + b2).squeeze(-1)
+    ref = s2 + upd.masked_fill(~mask, 0)  # dgmc.py:178-179
+    ref.backward(go.double())
+    assert torch.allclose(out.double(), ref, rtol=1e-5, atol=2e-5)
+    for a, b_ in zip(got, (s2, os2, ot2, w1, b1, w2, b2)):
+        scale = b_.grad.abs().max().item() + 1e-12
+        assert (a.double() - b_.grad).abs().max().item() <= 2e-5 * scale + 1e-6
+
+
+# ---------------------------------------------------------------------------------------------
+def _mean_agg(x, src, dst, n):
+    out = torch.zeros(n, x.size(1), dtype=x.dtype, device=x.device).index_add_(0, dst, x[src])
+    deg = torch.bincount(dst, minlength=n).clamp(min=1).to(x.dtype)
+    return out / deg.unsqueeze(1)
+
+
+@pytest.mark.parametrize('c', [4, 32, 64, 300, 10])
+def test_rel_aggregate(c):
+    from dgmc import ops
+    g = _gen(c)
+    n, e = 500, 2100
+    x = _randn(g, n, c).requires_grad_()
+    ei = torch.randint(n, (2, e), generator=g).to(DEV)
+    ei[:, :50] = 3  # self-loops on a hub + isolated nodes elsewhere
+    graph = ops.GraphCSR.of(ei, n)
+    cat = ops.rel_aggregate(x, graph)
+    go = _randn(g, n, 3 * c)
+    cat.backward(go)
+    xr = x.detach().double().requires_grad_()
+    ref = torch.cat([xr, _mean_agg(xr, ei[0], ei[1], n), _mean_agg(xr, ei[1], ei[0], n)], 1)
+    ref.backward(go.double())
+    assert torch.allclose(cat.double(), ref, rtol=1e-5, atol=1e-6)
+    assert torch.allclose(x.grad.double(), xr.grad, rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.parametrize('dim,cin,cout', [(2, 16, 32), (3, 16, 32), (1, 8, 8), (2, 12, 10)])
+def test_splineconv_matches_oracle(dim, cin, cout):
+    from dgmc.models.spline import SplineConv
+    from oracle import dgmc_oracle as O
+    g = _gen(dim * 100 + cin)
+    n, e = 100, 400
+    x = _randn(g, n, cin).requires_grad_()
+    ei = torch.randint(n, (2, e), generator=g).to(DEV)
+    pseudo = torch.rand(e, dim, generator=g).to(DEV)
+    pseudo[0] = 1.0  # closed end of the open spline: cell index wraps (torch_spline_conv modulo)
+    pseudo[1] = 0.0
+    conv = SplineConv(cin, cout, dim).to(DEV)
+    out = conv(x, ei, pseudo)
+    go = _randn(g, n, cout)
+    out.backward(go)
+    xr = x.detach().double().cpu().requires_grad_()
+    w, r, b = [p.detach().double().cpu().requires_grad_() for p in (conv.weight, conv.root, conv.bias)]
+    ref = O.splineconv(xr, ei.cpu(), pseudo.double().cpu(), w, r, b)
+    ref.backward(go.double().cpu())
+    assert torch.allclose(out.double().cpu(), ref, rtol=1e-5, atol=1e-5)
+    assert torch.allclose(x.grad.double().cpu(), xr.grad, rtol=1e-4, atol=1e-5)
+    assert torch.allclose(conv.weight.grad.double().cpu(), w.grad, rtol=1e-4, atol=1e-5)
+    assert torch.allclose(conv.root.grad.double().cpu(), r.grad, rtol=1e-4, atol=1e-5)
+    assert torch.allclose(conv.bias.grad.double().cpu(), b.grad, rtol=1e-4, atol=1e-5)
+
+
+def test_relcnn_matches_oracle_all_variants():
+    from itertools import product
+    from dgmc.models import RelCNN
+    from oracle import dgmc_oracle as O
+    g = _gen(5)
+    x = _randn(g, 100, 16)
+    ei = torch.randint(100, (2, 400), generator=g).to(DEV)
+    for cat, lin in product([False, True], [False, True]):  # test/models/test_rel.py:15-20
+        model = RelCNN(16, 32, 2, False, cat, lin, 0.0).to(DEV)
+        out = model(x, ei)
+        assert out.size() == (100, 16 + 2 * 32 if not lin and cat else 32)
+        assert out.size() == (100, model.out_channels)
+        spec = dict(kind='rel', out=32, layers=2, cat=cat, lin=lin, dropout=0.0)
+        spec['in'] = 16
+        p = {'psi.' + k: v.detach().double().cpu() for k, v in model.state_dict().items()}
+        ref = O.relcnn(x.double().cpu(), ei.cpu(), p, 'psi', spec)
+        assert torch.allclose(out.double().cpu(), ref, rtol=1e-5, atol=1e-5)
+    bn = RelCNN(16, 32, num_layers=2, batch_norm=True, cat=True, lin=True, dropout=0.5).to(DEV)
+    assert repr(bn) == 'RelCNN(16, 32, num_layers=2, batch_norm=True, cat=True, lin=True, dropout=0.5)'
+    assert repr(bn.convs[0]) == 'RelConv(16, 32)'
+    assert bn(x, ei).size() == (100, 32)
+
+
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize('B,ns,nt,c,k', [(1, 4, 4, 16, 4), (2, 50, 70, 32, 10), (1, 300, 500, 256, 25),
+                                         (1, 33, 40, 7, 40), (3, 20, 64, 64, 64)])
+def test_topk_simt_exact(B, ns, nt, c, k):
+    from dgmc import ops
+    g = _gen(ns * nt + k)
+    hs, ht = _randn(g, B, ns, c), _randn(g, B, nt, c)
+    idx, score = ops.topk_simt(hs, ht, k, want_scores=True)
+    full = hs.double() @ ht.double().transpose(1, 2)
+    ref_v, ref_i = full.topk(k, dim=2)
+    # index sets bit-exact wherever the k-th / (k+1)-th gap exceeds 1e-6 relative (north_star)
+    picked = torch.gather(full, 2, idx.long())
+    assert torch.allclose(picked, ref_v, rtol=1e-6, atol=1e-6)
+    if k < nt:
+        kth = full.topk(k + 1, dim=2)[0]
+        safe = (kth[..., k - 1] - kth[..., k]) > 1e-6 * kth[..., k - 1].abs()
+        same = (idx.long().sort(-1)[0] == ref_i.sort(-1)[0]).all(-1)
+        assert bool(same[safe].all())
+    assert torch.allclose(score.double(), picked, rtol=1e-5, atol=1e-5)
+    assert bool((score[..., :-1] >= score[..., 1:]).all())  # descending
