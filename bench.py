@@ -1,0 +1,388 @@
+#!/usr/bin/env python
+"""bench.py — DGMC forward+backward steps/s at the DBP15K shape (BASELINE.json `metric`).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+One step = what examples/dbp15k.py:37-47 does in its consensus phase (:68-69): zero_grad,
+forward(train mode, detach=True, k=10 (+10 negatives, ground truth included), num_steps=10),
+loss(S_L, train_y), backward, Adam step.  Workload = BASELINE.json configs[2]: a synthetic
+DBP15K zh_en-shaped pair (19,388 x 19,572 nodes, 300-d features, RelCNN 300->256 L3 / RelCNN
+64->64 L3).  Prints ONE JSON line (contract in the task statement).  `value` is measured with
+inputs resident in HBM; `e2e` through the public API with pinned HOST inputs copied every step
+and the loss read back.  `--impl reference` times the CPU oracle port of the reference
+(oracle/dgmc_oracle.py; the Python reference itself cannot travel to the GPU box).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, 'deep-graph-matching-consensus_b200')
+for _p in (ROOT, PKG):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import torch  # noqa: E402
+
+WORKLOAD = dict(name='DBP15K zh_en-shaped synthetic pair', n_s=19388, n_t=19572, feat=300,
+                e_s=70414, e_t=95142, dim=256, rnd_dim=64, layers=3, k=10, num_steps=10,
+                train_pairs=4500)
+METRIC = 'DGMC fwd+bwd steps/s at DBP15K shape'
+
+
+def make_inputs(w, seed=0):
+    """Seeded synthetic pair with planted structure: the first n_s target nodes are a permuted,
+    noisy copy of the source nodes, so top-k score gaps look like an alignment task rather than
+    pure-noise ties."""
+    g = torch.Generator().manual_seed(seed)
+    x_s = torch.randn(w['n_s'], w['feat'], generator=g)
+    perm = torch.randperm(w['n_t'], generator=g)[:w['n_s']]
+    x_t = torch.randn(w['n_t'], w['feat'], generator=g)
+    x_t[perm] = x_s + 0.5 * torch.randn(w['n_s'], w['feat'], generator=g)
+    e_s = torch.randint(w['n_s'], (2, w['e_s']), generator=g)
+    e_t = torch.randint(w['n_t'], (2, w['e_t']), generator=g)
+    rows = torch.sort(torch.randperm(w['n_s'], generator=g)[:w['train_pairs']])[0]
+    y = torch.stack([rows, perm[rows]])
+    return dict(x_s=x_s, e_s=e_s, x_t=x_t, e_t=e_t, y=y)
+
+
+class ClockSampler(object):
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    FIELDS = ('clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,'
+              'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,'
+              'clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(
+                ['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.FIELDS,
+                 '--format=csv,noheader,nounits', '-lms', '100'], stdout=subprocess.PIPE,
+                stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(',')])
+
+    def __exit__(self, *exc):
+        if self.proc is not None:
+            time.sleep(0.15)
+            self.proc.terminate()
+            self.thread.join(timeout=2)
+
+    def summary(self):
+        sm, mx, reasons = [], [], set()
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for n, v in zip(names, r[3:7]):
+                if v.lower().startswith('active'):
+                    reasons.add(n)
+        if not sm:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': [], 'samples': 0}
+        sm.sort()
+        return {'sm_mhz': sm[len(sm) // 2], 'sm_max_mhz': max(mx), 'reasons': sorted(reasons),
+                'samples': len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+# reference arm / cpu_baseline: the CPU oracle port of the reference
+# ------------------------------------------------------------------------------------------------
+def oracle_specs(w):
+    s1 = dict(kind='rel', out=w['dim'], layers=w['layers'], batch_norm=False, cat=True, lin=True,
+              dropout=0.5)
+    s1['in'] = w['feat']
+    s2 = dict(kind='rel', out=w['rnd_dim'], layers=w['layers'], batch_norm=False, cat=True, lin=True,
+              dropout=0.0)
+    s2['in'] = w['rnd_dim']
+    return s1, s2
+
+
+def cpu_reference_steps(w, inputs, steps, warmup, budget_s):
+    """Times the oracle port (reference algorithm, torch CPU ops, all host threads) on the same
+    workload.  Returns (steps_per_s, steps_timed, cores, seconds_per_step)."""
+    import torch.nn.functional as F
+    from oracle import dgmc_oracle as O
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    s1, s2 = oracle_specs(w)
+    params = {k: v.requires_grad_(True) for k, v in O.init_dgmc(0, s1, s2).items()}
+    opt = torch.optim.Adam(list(params.values()), lr=1e-3)
+    gen = torch.Generator().manual_seed(1)
+
+    def one_step():
+        opt.zero_grad()
+        neg = torch.randint(w['n_t'], (1, w['n_s'], min(w['k'], w['n_t'] - w['k'])), generator=gen)
+        draws = {'neg': neg, 'r_s': [torch.randn(1, w['n_s'], w['rnd_dim'], generator=gen)
+                                     for _ in range(w['num_steps'])]}
+        out = O.dgmc_forward(s1, s2, params, inputs['x_s'], inputs['e_s'], None, None,
+                             inputs['x_t'], inputs['e_t'], None, None, w['num_steps'], w['k'],
+                             y=inputs['y'], training=True, detach=True, draws=draws,
+                             dropout_fn=lambda x, p: F.dropout(x, p, True))
+        loss = O.loss(out['S_L'], inputs['y'], idx=out['idx'])
+        loss.backward()
+        opt.step()
+        return loss.item()
+
+    t0 = time.perf_counter()
+    one_step()  # warm-up (also sizes the sample)
+    first = time.perf_counter() - t0
+    for _ in range(max(0, min(warmup - 1, int(budget_s * 0.2 / max(first, 1e-3))))):
+        one_step()
+    n = max(1, min(steps, int(budget_s * 0.8 / max(first, 1e-3))))
+    t0 = time.perf_counter()
+    for _ in range(n):
+        one_step()
+    dt = (time.perf_counter() - t0) / n
+    return 1.0 / dt, n, cores, dt
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+def build_model(w, device):
+    from dgmc.models import DGMC, RelCNN
+    torch.manual_seed(0)
+    psi_1 = RelCNN(w['feat'], w['dim'], w['layers'], batch_norm=False, cat=True, lin=True, dropout=0.5)
+    psi_2 = RelCNN(w['rnd_dim'], w['rnd_dim'], w['layers'], batch_norm=False, cat=True, lin=True,
+                   dropout=0.0)
+    model = DGMC(psi_1, psi_2, num_steps=w['num_steps'], k=w['k'], detach=True).to(device)
+    model.train()
+    return model
+
+
+def train_step(model, opt, d):
+    opt.zero_grad(set_to_none=True)
+    _, S_L = model(d['x_s'], d['e_s'], None, None, d['x_t'], d['e_t'], None, None, d['y'])
+    loss = model.loss(S_L, d['y'])
+    loss.backward()
+    opt.step()
+    return loss
+
+
+def timed(fn, iters, flush=None):
+    """Average device time (ms) of fn over `iters` launches, CUDA events on the current stream;
+    `flush` (a >L2 buffer) is rewritten before every launch so each one starts with a cold L2."""
+    total = 0.0
+    for _ in range(iters):
+        if flush is not None:
+            flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        b.synchronize()
+        total += a.elapsed_time(b)
+    return total / iters
+
+
+def kernel_rooflines(w, model, d, peaks, step_ms):
+    """Times each hot kernel alone (cold L2) on step-shaped data; algorithmic bytes / flops per
+    launch follow SURVEY.md §8(d) (tables here are smaller than L2, so bytes_alg = bytes_min)."""
+    from dgmc import ops
+    dev = d['x_s'].device
+    n_s, n_t, C, R, k = w['n_s'], w['n_t'], w['dim'], w['rnd_dim'], w['k']
+    k_eff = k + min(k, n_t - k)
+    L, T = w['layers'], w['num_steps']
+    g = torch.Generator(device='cpu').manual_seed(3)
+    h_s = torch.randn(1, n_s, C, generator=g).to(dev)
+    h_t = torch.randn(1, n_t, C, generator=g).to(dev)
+    idx = torch.randint(n_t, (1, n_s, k_eff), generator=g).to(dev)
+    cand = ops.Candidates(idx, n_t)
+    cand.csr
+    S = torch.rand(n_s, k_eff, generator=g).to(dev)
+    r_s = torch.randn(n_s, R, generator=g).to(dev)
+    p_s, p_t = torch.randn(n_s, R, generator=g).to(dev), torch.randn(n_t, R, generator=g).to(dev)
+    w2, b2 = torch.randn(R, generator=g).to(dev), torch.zeros(1, device=dev)
+    graph_t = ops.GraphCSR.of(d['e_t'], n_t)
+    x_t = torch.randn(n_t, R, generator=g).to(dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    model_k = model.k
+    hbm, tf = peaks['hbm_gbs'], peaks['bf16_tflops']
+    rows = []
+
+    def add(name, fn, calls, unit_work, bound):
+        ms = timed(fn, 5, flush)
+        achieved = unit_work / (ms * 1e-3) / (1e12 if bound == 'tensor' else 1e9)
+        peak = tf if bound == 'tensor' else hbm
+        rows.append({'kernel': name, 'bound': bound, 'achieved': round(achieved, 2), 'peak': peak,
+                     'unit': 'TFLOP/s' if bound == 'tensor' else 'GB/s',
+                     'frac': round(achieved / peak, 4), 'traffic': None,
+                     'ms_per_launch': round(ms, 4), 'launches_per_step': calls,
+                     'share_of_step': round(ms * calls / step_ms, 4)})
+
+    with torch.no_grad():
+        add('K1 top-k (dgmc_topk_*)', lambda: model.__top_k__(h_s, h_t), 1,
+            2.0 * n_s * n_t * C, 'tensor')
+        add('K2 gather_dot', lambda: ops.gather_dot(h_s[0], h_t[0], cand), 1,
+            (n_s + n_t) * 4 * C + 8 * n_s * k_eff, 'hbm')
+        add('K3 softmax_k fwd', lambda: ops.softmax_k(S), T + 2, 8 * n_s * k_eff, 'hbm')
+        add('K4 transport (segment_gather by target)', lambda: ops.transport(S, r_s, cand), T,
+            8 * n_s * k_eff + 4 * R * (n_s + n_t), 'hbm')
+        add('K5 rel_aggregate (2 segment_gathers, target graph)',
+            lambda: ops.rel_aggregate(x_t, graph_t), 2 * L * T,
+            8 * n_t * R + 8 * w['e_t'] + 8 * n_t, 'hbm')
+        add('K6 diff_mlp fwd', lambda: ops.diff_mlp(S, p_s, p_t, w2, b2, cand), T,
+            4 * R * (n_s + n_t) + 12 * n_s * k_eff, 'hbm')
+    model.k = model_k
+    return rows
+
+
+def load_peaks():
+    path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(path):
+        p = json.load(open(path))
+        return {'hbm_gbs': p['hbm_gbs'], 'bf16_tflops': p['bf16_tflops'],
+                'bf16_tflops_sustained': p.get('bf16_tflops_sustained'), 'source': 'measured'}
+    return {'hbm_gbs': 6650.0, 'bf16_tflops': 1590.0, 'bf16_tflops_sustained': 1400.0,
+            'source': 'fallback'}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=20)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    ap.add_argument('--cpu-budget', type=float, default=None, help='seconds of CPU baseline work')
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == 'b200' else args.warmup
+
+    rank = int(os.environ.get('RANK', 0))
+    world = int(os.environ.get('WORLD_SIZE', 1))
+    local = int(os.environ.get('LOCAL_RANK', 0))
+    w = dict(WORKLOAD)
+    config = {'workload': '%s: %d x %d nodes, %d-d, RelCNN(%d,%d,L%d)/RelCNN(%d,%d,L%d), sparse k=%d '
+              '(+%d negatives), %d consensus steps, detach=True, %d train pairs; step = fwd + '
+              'loss + bwd + Adam' % (w['name'], w['n_s'], w['n_t'], w['feat'], w['feat'], w['dim'],
+                                     w['layers'], w['rnd_dim'], w['rnd_dim'], w['layers'], w['k'],
+                                     w['k'], w['num_steps'], w['train_pairs']),
+              'baseline_config': 'BASELINE.json configs[2]'}
+
+    if args.impl == 'reference':
+        if rank != 0:
+            return 0
+        inputs = make_inputs(w)
+        budget = args.cpu_budget or 150.0
+        sps, n, cores, dt = cpu_reference_steps(w, inputs, args.steps, args.warmup, budget)
+        sample = ('%d full steps of the same workload (oracle port of the reference: torch CPU '
+                  'ops, row-chunked matmul+topk for __top_k__), %d threads' % (n, cores))
+        print(json.dumps({
+            'impl': 'reference', 'metric': METRIC, 'value': sps, 'unit': 'steps/s', 'n_gpus': 0,
+            'steps': n, 'warmup': 1, 'ms_per_step': dt * 1e3, 'higher_is_better': True,
+            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'config': config,
+            'cpu_baseline': {'value': sps, 'unit': 'steps/s', 'cores': cores, 'kind': 'port',
+                             'sample': sample},
+            'e2e': {'value': sps, 'unit': 'steps/s', 'h2d_bytes_per_step': 0,
+                    'd2h_bytes_per_step': 0}}))
+        return 0
+
+    import torch.distributed as dist
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    from dgmc import native
+
+    host = make_inputs(w)
+    pinned = {k: v.pin_memory() for k, v in host.items()}
+    d = {k: v.to(dev) for k, v in host.items()}
+    model = build_model(w, dev)
+    opt = torch.optim.Adam([p for p in model.parameters()], lr=1e-3)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- resident-input timing ------------------------------------------------------------
+    for _ in range(args.warmup):
+        train_step(model, opt, d)
+    barrier()
+    launches0 = native.lib.dgmc_launch_count()
+    with ClockSampler(local) as clocks:
+        start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        start.record()
+        for _ in range(args.steps):
+            loss = train_step(model, opt, d)
+        end.record()
+        barrier()
+    ms = torch.tensor([start.elapsed_time(end)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_per_step = ms.item() / args.steps
+    launches = (native.lib.dgmc_launch_count() - launches0) // args.steps
+    value = world * 1e3 / ms_per_step  # replicas: every rank runs the whole pair
+
+    # ---- end-to-end: pinned host inputs copied every step, loss read back -----------------
+    h2d = sum(v.numel() * v.element_size() for v in pinned.values())
+    for _ in range(2):
+        for k_, v in pinned.items():
+            d[k_].copy_(v, non_blocking=True)
+        train_step(model, opt, d).item()
+    barrier()
+    start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    start.record()
+    for _ in range(args.steps):
+        for k_, v in pinned.items():
+            d[k_].copy_(v, non_blocking=True)
+        loss_value = train_step(model, opt, d).item()
+    end.record()
+    barrier()
+    ms2 = torch.tensor([start.elapsed_time(end)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms2, op=dist.ReduceOp.MAX)
+    e2e_value = world * 1e3 / (ms2.item() / args.steps)
+
+    out = None
+    if rank == 0:
+        peaks = load_peaks()
+        rl = kernel_rooflines(w, model, d, peaks, ms_per_step)
+        top = max(rl, key=lambda r: r['share_of_step'])
+        roofline = {k_: top[k_] for k_ in ('bound', 'achieved', 'peak', 'unit', 'frac', 'traffic')}
+        roofline.update(kernel=top['kernel'], peak_source=peaks['source'] + ' (burst: kernel timed alone)')
+        out = {
+            'metric': METRIC, 'value': value, 'unit': 'steps/s', 'n_gpus': world, 'steps': args.steps,
+            'warmup': args.warmup, 'ms_per_step': ms_per_step, 'higher_is_better': True,
+            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'config': dict(config, parallelism='replicas x%d' % world if world > 1 else 'single GPU',
+                           l2='working set per step (inputs + saved activations, ~1 GB) exceeds the '
+                              '126 MB L2; per-kernel roofline timings flush L2 with a 256 MB write'),
+            'clocks': clocks.summary(),
+            'e2e': {'value': e2e_value, 'unit': 'steps/s', 'h2d_bytes_per_step': h2d,
+                    'd2h_bytes_per_step': 4},
+            'gpu_launches': int(launches), 'final_loss': loss_value,
+            'roofline': roofline, 'roofline_all': rl,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            sps, n, cores, dt = cpu_reference_steps(w, host, 2, 1, args.cpu_budget or 30.0)
+            out['cpu_baseline'] = {
+                'value': sps, 'unit': 'steps/s', 'cores': cores, 'kind': 'port',
+                'sample': '%d full step(s) of the same workload after 1 warm-up, oracle port of the '
+                          'reference (torch CPU, chunked matmul+topk), %.1f s/step' % (n, dt)}
+        print(json.dumps(out))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == '__main__':
+    sys.exit(main())

@@ -14,7 +14,10 @@ namespace dgmc {
 
 void set_error(const char* fmt, ...);  // thread-local message, read by dgmc_last_error()
 
-inline int check_launch(const char* what) {
+void count_launches(int n);  // process-wide tally of kernels launched by this library
+
+inline int check_launch(const char* what, int kernels = 1) {
+    count_launches(kernels);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         set_error("%s: %s", what, cudaGetErrorString(e));

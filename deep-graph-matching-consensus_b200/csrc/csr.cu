@@ -252,5 +252,5 @@ extern "C" int dgmc_csr_build(const int32_t* keys, int64_t nnz, int64_t n_seg, i
         src_v = dst_v;
     }
     boundaries_kernel<<<wave_grid(nnz + 1, 256, 4), 256, 0, stream>>>(src_k, nnz, n_seg, ptr);
-    return check_launch("csr_build");
+    return check_launch("csr_build", 5 * passes + 1);
 }

@@ -250,5 +250,5 @@ extern "C" int dgmc_dense_consensus_bwd(const float* g, const float* ps, const f
 #undef K_S
 #undef K_T
     dense_finish_kernel<<<(r + 256) / 256, 256, 0, stream>>>(partial, grid_s, r, d_w2, d_b2);
-    return check_launch("dense_consensus_bwd");
+    return check_launch("dense_consensus_bwd", 3);
 }

@@ -275,7 +275,7 @@ extern "C" int dgmc_diff_mlp_bwd_rows(const float* g, const float* ps, const flo
     float* partial = (float*)workspace;
     DM_DISPATCH(diff_mlp_bwd_rows_kernel, grid, smem, g, ps, pt, idx, w2, d_ps, partial, m, k, r4);
     diff_mlp_bwd_finish_kernel<<<(r + 256) / 256, 256, 0, stream>>>(partial, grid, r, d_w2, d_b2);
-    return check_launch("diff_mlp_bwd_rows");
+    return check_launch("diff_mlp_bwd_rows", 2);
 }
 
 extern "C" int dgmc_diff_mlp_bwd_targets(const float* g, const float* ps, const float* pt,

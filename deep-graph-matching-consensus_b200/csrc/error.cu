@@ -12,7 +12,13 @@ void set_error(const char* fmt, ...) {
     vsnprintf(g_err, sizeof(g_err), fmt, ap);
     va_end(ap);
 }
+static unsigned long long g_launches = 0;
+void count_launches(int n) { __atomic_fetch_add(&g_launches, (unsigned long long)n, __ATOMIC_RELAXED); }
 }  // namespace dgmc
+
+extern "C" uint64_t dgmc_launch_count(void) {
+    return __atomic_load_n(&dgmc::g_launches, __ATOMIC_RELAXED);
+}
 
 extern "C" const char* dgmc_last_error(void) { return dgmc::g_err; }
 extern "C" int dgmc_abi_version(void) { return DGMC_B200_ABI_VERSION; }

@@ -18,7 +18,7 @@ HEADER_PATH = os.path.join(REPO_ROOT, 'include', 'dgmc_b200.h')
 
 _CTYPES = {
     'int': ctypes.c_int, 'int64_t': ctypes.c_int64, 'size_t': ctypes.c_size_t,
-    'float': ctypes.c_float, 'dgmc_stream_t': ctypes.c_void_p,
+    'float': ctypes.c_float, 'dgmc_stream_t': ctypes.c_void_p, 'uint64_t': ctypes.c_uint64,
 }
 
 

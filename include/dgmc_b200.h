@@ -32,6 +32,8 @@ typedef struct CUstream_st* dgmc_stream_t; /* == cudaStream_t */
 
 const char* dgmc_last_error(void);
 int dgmc_abi_version(void);
+/* number of CUDA kernels this library has launched in this process (bench.py's gpu_launches) */
+uint64_t dgmc_launch_count(void);
 
 /* ---- K1 (small shapes): exact fp32 top-k, one warp per source row ------------------------
  * idx_out[b, i, 0:k] = columns j of the k largest <h_s[b,i,:], h_t[b,j,:]>, descending, ties by
