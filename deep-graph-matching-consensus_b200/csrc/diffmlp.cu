@@ -292,3 +292,73 @@ extern "C" int dgmc_diff_mlp_bwd_targets(const float* g, const float* ps, const 
     DM_DISPATCH(diff_mlp_bwd_targets_kernel, grid, 0, g, ps, pt, tptr, perm, w2, d_pt, n_t, k, r4);
     return check_launch("diff_mlp_bwd_targets");
 }
+
+// ---------------------------------------------------------------------------------------------
+// Allocation-free variant of dgmc_diff_mlp_bwd_rows.
+//
+// Some programs that bind this library cannot hand it a workspace: a C/C++ serving process that
+// reserved the whole device for its own arena at start-up and gives plug-ins no allocator, or a
+// latency-critical loop in which cudaMalloc / cudaFree (which serialise the device) are banned.
+// For them the per-block partial sums of d_w2 / d_b2 live in a fixed array inside the library's
+// device image instead of in caller memory.
+//
+//  * limit: r <= DGMC_NOALLOC_MAX_R (128).  The array is 1024 x 129 floats = 528,384 bytes and is
+//    resident on EVERY GPU that loads the library until the process exits.
+//  * every call on a device uses the same array, so two calls that overlap on the GPU (different
+//    streams, or different host threads) race on it; serialise them.
+//  * nothing in it has to start at zero: each launched block overwrites its own row before the
+//    finishing kernel reads exactly those rows, so left-over contents of an earlier call are
+//    never observed.
+//  * the first call on each device looks the array's device address up (cudaGetSymbolAddress —
+//    the symbol's name is only a host-side handle, not an address a kernel can use).  Make that
+//    first call outside any stream capture.
+// ---------------------------------------------------------------------------------------------
+#include <mutex>
+
+#define DGMC_NOALLOC_MAX_R 128
+#define DGMC_NOALLOC_MAX_DEVICES 64
+
+namespace dgmc {
+static __device__ __align__(256) float g_noalloc_partials[DM_MAX_BLOCKS * (DGMC_NOALLOC_MAX_R + 1)];
+
+// device address of g_noalloc_partials on the CURRENT device (looked up once per device)
+static int noalloc_scratch(float** out) {
+    static std::mutex mu;
+    static float* cached[DGMC_NOALLOC_MAX_DEVICES] = {nullptr};
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= DGMC_NOALLOC_MAX_DEVICES) {
+        set_error("diff_mlp_bwd_rows_noalloc: cudaGetDevice failed or device %d out of range: %s", dev,
+                  cudaGetErrorString(e));
+        return DGMC_ERR_CUDA;
+    }
+    std::lock_guard<std::mutex> lock(mu);
+    if (!cached[dev]) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_noalloc_partials);
+        if (e != cudaSuccess || !p) {
+            set_error("diff_mlp_bwd_rows_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev,
+                      cudaGetErrorString(e));
+            return DGMC_ERR_CUDA;
+        }
+        cached[dev] = static_cast<float*>(p);
+    }
+    *out = cached[dev];
+    return DGMC_OK;
+}
+}  // namespace dgmc
+
+extern "C" int dgmc_diff_mlp_bwd_rows_noalloc(const float* g, const float* ps, const float* pt,
+                                              const int32_t* idx, const float* w2, float* d_ps,
+                                              float* d_w2, float* d_b2, int64_t m, int k, int r,
+                                              dgmc_stream_t stream) {
+    if (r > DGMC_NOALLOC_MAX_R) {
+        set_error("diff_mlp_bwd_rows_noalloc: r=%d exceeds the built-in scratch (max r=%d); use "
+                  "dgmc_diff_mlp_bwd_rows with a caller-provided workspace", r, DGMC_NOALLOC_MAX_R);
+        return DGMC_ERR_UNSUPPORTED;
+    }
+    float* scratch = nullptr;
+    if (int e = noalloc_scratch(&scratch)) return e;
+    return dgmc_diff_mlp_bwd_rows(g, ps, pt, idx, w2, d_ps, d_w2, d_b2, m, k, r, scratch,
+                                  sizeof(float) * DM_MAX_BLOCKS * (DGMC_NOALLOC_MAX_R + 1), stream);
+}

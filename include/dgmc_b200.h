@@ -107,6 +107,17 @@ int dgmc_diff_mlp_bwd_rows(const float* g, const float* ps, const float* pt, con
                            const float* w2, float* d_ps, float* d_w2, float* d_b2, int64_t m,
                            int k, int r, void* workspace, size_t workspace_bytes,
                            dgmc_stream_t stream);
+/* Same computation and outputs as dgmc_diff_mlp_bwd_rows, for callers that cannot supply a
+ * workspace (a host process that owns all device memory through its own arena and gives plug-ins
+ * no allocator, or a loop where cudaMalloc/cudaFree are banned because they serialise the device).
+ * No counterpart in the reference.  The partial sums live in a 528,384-byte array inside the
+ * library (held by every GPU that loads it until exit); r must be <= 128, larger r returns
+ * DGMC_ERR_UNSUPPORTED.  All calls on a device share that array: calls that overlap on the GPU
+ * race.  The first call on each device resolves the array's device address — make it outside
+ * any stream capture. */
+int dgmc_diff_mlp_bwd_rows_noalloc(const float* g, const float* ps, const float* pt,
+                                   const int32_t* idx, const float* w2, float* d_ps, float* d_w2,
+                                   float* d_b2, int64_t m, int k, int r, dgmc_stream_t stream);
 /* backward, target side (by-target CSR of idx: tptr/perm from dgmc_csr_build):
  * d_pt[t, c] = -w2[c] * sum_{e in seg(t)} g[perm[e]] * [ps[perm[e]/k, c] > pt[t, c]]. */
 int dgmc_diff_mlp_bwd_targets(const float* g, const float* ps, const float* pt,
