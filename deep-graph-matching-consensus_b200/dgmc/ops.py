@@ -419,12 +419,27 @@ def dense_consensus(s_hat, ps, pt, w2, b2, sm, tm):
 # K1
 # --------------------------------------------------------------------------------------------
 def topk_tensor_core_ok(h_s, h_t, k):
-    """Whether the tcgen05 streaming top-k kernel supports this shape."""
-    return False
+    """Whether the tcgen05 streaming top-k kernel supports this shape (dgmc_b200.h)."""
+    _, n_s, c = h_s.shape
+    n_t = h_t.size(1)
+    return n_s >= 128 and n_t >= 128 and bool(query('dgmc_topk_tc_supported', n_s, n_t, c, k))
 
 
-def topk_tensor_core(h_s, h_t, k):
-    raise native.DgmcNativeError('tensor-core top-k not built')
+def topk_tensor_core(h_s, h_t, k, want_scores=False):
+    """h_s [B, N_s, C], h_t [B, N_t, C] -> int32 [B, N_s, k] via the tcgen05/TMA kernel (one call
+    per graph pair; sparse matching is single-pair in every reference script)."""
+    h_s, h_t = _f32(h_s), _f32(h_t)
+    B, n_s, c = h_s.shape
+    n_t = h_t.size(1)
+    idx = torch.empty(B, n_s, k, dtype=torch.int32, device=h_s.device)
+    score = torch.empty(B, n_s, k, dtype=torch.float32, device=h_s.device) if want_scores else None
+    ws = _workspace(query('dgmc_topk_tc_workspace', n_s, n_t, c, k) + 256, h_s.device)
+    off = (-ws.data_ptr()) % 256
+    ws = ws[off:]
+    for b in range(B):
+        call('dgmc_topk_tc', h_s[b], c, h_t[b], c, n_s, n_t, c, k, idx[b],
+             None if score is None else score[b], ws, ws.numel(), stream_ptr())
+    return (idx, score) if want_scores else idx
 
 
 def topk_simt(h_s, h_t, k, want_scores=False):

@@ -35,6 +35,20 @@ int dgmc_abi_version(void);
 /* number of CUDA kernels this library has launched in this process (bench.py's gpu_launches) */
 uint64_t dgmc_launch_count(void);
 
+/* ---- K1: streaming top-k on the tensor cores -----------------------------------------------
+ * idx_out[i, 0:k] = columns j of the k largest <h_s[i,:], h_t[j,:]>, descending by exact fp32
+ * score, ties by ascending j; score_out (nullable) those fp32 scores.  One graph pair per call.
+ * replaces DGMC.__top_k__ (dgmc.py:85-94: KeOps argKmin, else broadcast-mul-sum + topk).
+ * bf16 tcgen05 GEMM fed by TMA with a fused per-row selection of k' = 16 or 32 candidates in the
+ * epilogue (the N_s x N_t scores never reach HBM), stream-K work split, then an fp32 re-scoring of
+ * the k' survivors.  Supported: c <= 512, 1 <= k <= 26, k <= n_t (dgmc_topk_tc_supported() != 0).
+ * The workspace (bf16 operand copies + partial candidate lists) must be 256-byte aligned. */
+int dgmc_topk_tc_supported(int n_s, int n_t, int c, int k);
+size_t dgmc_topk_tc_workspace(int n_s, int n_t, int c, int k);
+int dgmc_topk_tc(const float* h_s, int64_t lds, const float* h_t, int64_t ldt, int n_s, int n_t, int c,
+                 int k, int32_t* idx_out, float* score_out, void* workspace, size_t workspace_bytes,
+                 dgmc_stream_t stream);
+
 /* ---- K1 (small shapes): exact fp32 top-k, one warp per source row ------------------------
  * idx_out[b, i, 0:k] = columns j of the k largest <h_s[b,i,:], h_t[b,j,:]>, descending, ties by
  * ascending j (graph-local column ids); score_out (nullable) the fp32 scores.
