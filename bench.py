@@ -261,6 +261,9 @@ def main():
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--cpu-budget', type=float, default=None, help='seconds of CPU baseline work')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--profile-eager', action='store_true',
+                    help='warm up, run --steps eager steps inside the NVTX range "timed_step" and exit '
+                         '(for ncu --nvtx --nvtx-include "timed_step/")')
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == 'b200' else args.warmup
 
@@ -305,45 +308,72 @@ def main():
     pinned = {k: v.pin_memory() for k, v in host.items()}
     d = {k: v.to(dev) for k, v in host.items()}
     model = build_model(w, dev)
-    opt = torch.optim.Adam([p for p in model.parameters()], lr=1e-3)
+    opt = torch.optim.Adam([p for p in model.parameters()], lr=1e-3, capturable=True)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- resident-input timing ------------------------------------------------------------
+    if args.profile_eager:
+        for _ in range(args.warmup):
+            train_step(model, opt, d)
+        torch.cuda.synchronize()
+        torch.cuda.nvtx.range_push('timed_step')
+        for _ in range(args.steps):
+            train_step(model, opt, d)
+        torch.cuda.synchronize()
+        torch.cuda.nvtx.range_pop()
+        print(json.dumps({'profile_eager_steps': args.steps}))
+        return 0
+
+    from dgmc.utils import GraphedTrainStep
+    args_of = lambda t: (t['x_s'], t['e_s'], None, None, t['x_t'], t['e_t'], None, None, t['y'])  # noqa: E731
+
+    # ---- eager step (plain Python loop over the public API), for reference ------------------
     for _ in range(args.warmup):
         train_step(model, opt, d)
     barrier()
     launches0 = native.lib.dgmc_launch_count()
+    n_eager = max(2, min(5, args.steps))
+    start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    start.record()
+    for _ in range(n_eager):
+        train_step(model, opt, d)
+    end.record()
+    barrier()
+    eager_ms = start.elapsed_time(end) / n_eager
+    launches = (native.lib.dgmc_launch_count() - launches0) // n_eager
+
+    # ---- resident inputs: the whole step captured in one CUDA graph -------------------------
+    graphed = GraphedTrainStep(model, opt, *args_of(d), structure_is_static=True)
+    for _ in range(args.warmup):
+        graphed(*args_of(d))
+    barrier()
     with ClockSampler(local) as clocks:
         start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         start.record()
         for _ in range(args.steps):
-            loss = train_step(model, opt, d)
+            graphed(*args_of(d))
         end.record()
         barrier()
     ms = torch.tensor([start.elapsed_time(end)], device=dev)
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms_per_step = ms.item() / args.steps
-    launches = (native.lib.dgmc_launch_count() - launches0) // args.steps
     value = world * 1e3 / ms_per_step  # replicas: every rank runs the whole pair
 
-    # ---- end-to-end: pinned host inputs copied every step, loss read back -----------------
+    # ---- end-to-end: pinned host inputs copied every step (graph structure rebuilt inside the
+    #      captured step), loss read back --------------------------------------------------------
     h2d = sum(v.numel() * v.element_size() for v in pinned.values())
-    for _ in range(2):
-        for k_, v in pinned.items():
-            d[k_].copy_(v, non_blocking=True)
-        train_step(model, opt, d).item()
+    e2e_step = GraphedTrainStep(model, opt, *args_of(d), structure_is_static=False)
+    for _ in range(3):
+        e2e_step(*args_of(pinned)).item()
     barrier()
     start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     start.record()
     for _ in range(args.steps):
-        for k_, v in pinned.items():
-            d[k_].copy_(v, non_blocking=True)
-        loss_value = train_step(model, opt, d).item()
+        loss_value = e2e_step(*args_of(pinned)).item()
     end.record()
     barrier()
     ms2 = torch.tensor([start.elapsed_time(end)], device=dev)
@@ -363,12 +393,16 @@ def main():
             'warmup': args.warmup, 'ms_per_step': ms_per_step, 'higher_is_better': True,
             'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
             'config': dict(config, parallelism='replicas x%d' % world if world > 1 else 'single GPU',
+                           execution='whole step (zero_grad+fwd+loss+bwd+Adam) replayed as one CUDA '
+                                     'graph (dgmc.utils.GraphedTrainStep); eager_ms_per_step is the '
+                                     'same step issued from Python',
                            l2='working set per step (inputs + saved activations, ~1 GB) exceeds the '
                               '126 MB L2; per-kernel roofline timings flush L2 with a 256 MB write'),
             'clocks': clocks.summary(),
             'e2e': {'value': e2e_value, 'unit': 'steps/s', 'h2d_bytes_per_step': h2d,
                     'd2h_bytes_per_step': 4},
             'gpu_launches': int(launches), 'final_loss': loss_value,
+            'eager_ms_per_step': eager_ms,
             'roofline': roofline, 'roofline_all': rl,
         }
         if world == 1 and not args.no_cpu_baseline:

@@ -96,21 +96,18 @@ class DGMC(torch.nn.Module):
 
     def __include_gt__(self, S_idx, s_mask, y):
         """Make sure y[1] is among the candidates of row y[0]: rows that miss it get their LAST
-        slot overwritten (dgmc.py:96-112).  Like the reference this assumes y[0] ascending."""
+        slot overwritten (dgmc.py:96-112).  The reference does this with a masked_scatter that is
+        only right when y[0] is ascending and duplicate-free; for such y
+        this gives the same result, with static shapes (no nonzero / host sync, so the step can be
+        captured in a CUDA graph).  For other y each listed row simply receives ITS ground truth."""
         B, n_s, k = S_idx.shape
         rows, cols = y[0], y[1]
         flat = S_idx.reshape(B * n_s, k)
-        if s_mask is not None and not bool(s_mask.all()):
-            real = torch.nonzero(s_mask.view(-1)).view(-1)  # flat real-node index -> padded row
-        else:
-            real = None
-        padded_rows = rows if real is None else real[rows]
-        missing = (flat[padded_rows] != cols.view(-1, 1)).all(dim=-1)
-        flag = torch.zeros(B * n_s, dtype=torch.bool, device=S_idx.device)
-        flag[padded_rows] = missing
-        targets = torch.nonzero(flag).view(-1)  # ascending, as masked_scatter visits them
+        if s_mask is not None:  # flat real-node index -> padded row (batched graphs only)
+            rows = torch.nonzero(s_mask.view(-1)).view(-1)[rows]
+        missing = (flat[rows] != cols.view(-1, 1)).all(dim=-1)
         out = flat.clone()
-        out[targets, k - 1] = cols[missing][:targets.numel()]
+        out[rows, k - 1] = torch.where(missing, cols, flat[rows, k - 1])
         return out.view(B, n_s, k)
 
     # ---------------------------------------------------------------------------------------
@@ -141,10 +138,21 @@ class DGMC(torch.nn.Module):
         w1, b1, w2, b2 = self._hoisted_mlp()
         num_steps = self.num_steps or 0
 
+        merged = ops.MergedPair.of(self.psi_2, self.training, edge_index_s, edge_index_t,
+                                   edge_attr_s, edge_attr_t, x_s.size(0), x_t.size(0))
+
         def consensus_nodes(r_s, r_t):
             """psi_2 on both graphs, then the hoisted first MLP layer -> (P_s, P_t) flat."""
-            o_s = self.psi_2(_rows(r_s, s_mask), edge_index_s, edge_attr_s)
-            o_t = self.psi_2(_rows(r_t, t_mask), edge_index_t, edge_attr_t)
+            r_s, r_t = _rows(r_s, s_mask), _rows(r_t, t_mask)
+            if merged is not None:
+                # psi_2 shares its weights between the two graphs: run it ONCE on their disjoint
+                # union (same arithmetic per node, half the launches, twice the GEMM height)
+                o = self.psi_2(torch.cat([r_s, r_t], dim=0), merged.edge_index, merged.edge_attr)
+                p = o @ w1.t()
+                p_s, p_t = p[:r_s.size(0)] + b1, p[r_s.size(0):]
+                return _repad(p_s, s_mask), _repad(p_t, t_mask)
+            o_s = self.psi_2(r_s, edge_index_s, edge_attr_s)
+            o_t = self.psi_2(r_t, edge_index_t, edge_attr_t)
             o_s, o_t = _repad(o_s, s_mask), _repad(o_t, t_mask)
             return torch.addmm(b1, o_s, w1.t()), o_t @ w1.t()
 
@@ -209,6 +217,13 @@ class DGMC(torch.nn.Module):
         else:
             assert S.__idx__ is not None and S.__val__ is not None
             hit = S.__idx__[y[0]] == y[1].view(-1, 1)
+            if reduction != 'none':
+                # same value as indexing with the boolean mask (every hit entry counts once,
+                # ground truths absent from the candidate list are dropped), but with static
+                # shapes: no nonzero, no host sync
+                nll = -torch.log(S.__val__[y[0]] + EPS)
+                total = (nll * hit).sum()
+                return total if reduction == 'sum' else total / hit.sum()
             val = S.__val__[y[0]][hit]
         nll = -torch.log(val + EPS)
         return nll if reduction == 'none' else getattr(torch, reduction)(nll)

@@ -86,6 +86,49 @@ class GraphCSR(object):
         return hit[1]
 
 
+class MergedPair(object):
+    """Disjoint union of the source and the target graph (target node ids shifted by N_s), so that
+    a weight-sharing psi can process both in one pass.  Only used when that is arithmetically
+    identical to two separate calls AND draws no random numbers: psi must be this package's
+    RelCNN / SplineCNN without active batch-norm statistics or dropout."""
+    _cache = {}
+
+    def __init__(self, e_s, e_t, ea_s, ea_t, n_s):
+        self.edge_index = torch.cat([e_s, e_t + n_s], dim=1)
+        self.edge_attr = None if ea_s is None else torch.cat([ea_s, ea_t], dim=0)
+
+    @staticmethod
+    def mergeable(psi, training):
+        from .models.rel import RelCNN
+        from .models.spline import SplineCNN
+        if not isinstance(psi, (RelCNN, SplineCNN)):
+            return False
+        if training and (getattr(psi, 'batch_norm', False) or psi.dropout > 0):
+            return False
+        return True
+
+    @classmethod
+    def of(cls, psi, training, e_s, e_t, ea_s, ea_t, n_s, n_t):
+        if not cls.mergeable(psi, training) or (ea_s is None) != (ea_t is None):
+            return None
+        tensors = [t for t in (e_s, e_t, ea_s, ea_t) if t is not None]
+        key = tuple((t.data_ptr(), tuple(t.shape), t._version) for t in tensors) + (n_s, n_t)
+        hit = cls._cache.get(key)
+        if hit is None or any(a is not b for a, b in zip(hit[0], tensors)):
+            if len(cls._cache) > 64:
+                cls._cache.clear()
+            hit = (tensors, cls(e_s, e_t, ea_s, ea_t, n_s))
+            cls._cache[key] = hit
+        return hit[1]
+
+
+def clear_caches():
+    """Forget cached graph structures (CSR, spline bases, merged pairs)."""
+    GraphCSR._cache.clear()
+    SplineBasis._cache.clear()
+    MergedPair._cache.clear()
+
+
 class Candidates(object):
     """The sparse correspondence structure of one forward pass: S_idx (dgmc.py:186-195) as flat
     int32 target rows plus its by-target CSR (dgmc_csr_build), shared by K2/K4/K6 and their

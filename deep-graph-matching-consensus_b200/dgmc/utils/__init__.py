@@ -1,3 +1,4 @@
 from .data import PairDataset, ValidPairDataset, PairData
+from .graphed import GraphedTrainStep
 
-__all__ = ['PairDataset', 'ValidPairDataset']
+__all__ = ['PairDataset', 'ValidPairDataset', 'GraphedTrainStep']

@@ -1,0 +1,67 @@
+"""CUDA-graph capture of a whole DGMC training step (no counterpart in the reference, which
+launches ~100 small kernels per consensus step from Python and is launch-bound on a B200).
+
+At the DBP15K shape one step is ~1,000 kernel launches of 5-100 us each; issued eagerly from Python
+the GPU waits on the host.  `GraphedTrainStep` captures zero_grad + forward + loss + backward +
+optimizer step once and replays it with one launch.  What makes that possible: the sparse
+path has static shapes and no host synchronisation (`__include_gt__` and `loss` avoid nonzero),
+every kernel of libdgmc_b200 is stream-ordered on the current stream and allocates nothing, and
+the random draws use torch's graph-safe Philox generator, so each replay draws fresh indicators
+and negatives.
+
+    step = GraphedTrainStep(model, optimizer, x_s, e_s, None, None, x_t, e_t, None, None, y)
+    loss = step(x_s, e_s, None, None, x_t, e_t, None, None, y)   # tensors may live on the host
+
+Inputs are copied into static device buffers on every call (host tensors should be pinned);
+shapes must match the example.  `structure_is_static=True` additionally treats edge_index /
+edge_attr as fixed (their CSR is built once, outside the graph) — the analogue of the reference
+training on one fixed pair for 200 epochs (examples/dbp15k.py:63-76).
+"""
+import torch
+
+from .. import ops
+
+
+class GraphedTrainStep(object):
+    def __init__(self, model, optimizer, *example_inputs, loss_fn=None, warmup=3,
+                 structure_is_static=False):
+        for group in optimizer.param_groups:
+            if 'capturable' in group and not group['capturable']:
+                raise ValueError('GraphedTrainStep needs an optimizer built with capturable=True')
+        self.model, self.optimizer = model, optimizer
+        self.loss_fn = loss_fn or (lambda S_0, S_L, y: model.loss(S_L, y))
+        dev = next(model.parameters()).device
+        self.static = [None if t is None else t.to(dev).clone() for t in example_inputs]
+        self.structure_is_static = structure_is_static
+        self.graph = torch.cuda.CUDAGraph()
+
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(warmup):
+                self._step()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        if not structure_is_static:
+            ops.clear_caches()  # so that the CSR builds are captured and re-run on new inputs
+        with torch.cuda.graph(self.graph):
+            self.loss = self._step()
+        if not structure_is_static:
+            ops.clear_caches()  # entries made during capture point into the graph's private pool
+
+    def _step(self):
+        self.optimizer.zero_grad(set_to_none=True)
+        S_0, S_L = self.model(*self.static)
+        loss = self.loss_fn(S_0, S_L, self.static[-1])
+        loss.backward()
+        self.optimizer.step()
+        return loss.detach()
+
+    def __call__(self, *inputs):
+        """Copy the inputs into the captured buffers and replay.  Returns the (static) loss tensor;
+        reading it with .item() is the only host synchronisation."""
+        for dst, src in zip(self.static, inputs):
+            if dst is not None and src is not dst:
+                dst.copy_(src, non_blocking=True)
+        self.graph.replay()
+        return self.loss
