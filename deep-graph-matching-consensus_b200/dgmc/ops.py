@@ -35,9 +35,26 @@ def csr_build(keys, n_seg):
     return ptr, perm
 
 
+def csr_blocks(ptr, n_seg, nnz):
+    """block_seg[b] = segment of entry b * DGMC_CSR_BLOCK (work list of the balanced kernels)."""
+    nblk = (nnz + CSR_BLOCK - 1) // CSR_BLOCK
+    blocks = torch.empty(max(nblk, 1), dtype=torch.int32, device=ptr.device)
+    if nnz > 0:
+        call('dgmc_csr_blocks', ptr, n_seg, nnz, blocks, stream_ptr())
+    return blocks
+
+
+CSR_BLOCK = 32  # DGMC_CSR_BLOCK in include/dgmc_b200.h
+
+
+def _vec_ok(t):
+    return t.size(1) % 4 == 0 and t.stride(0) % 4 == 0 and t.data_ptr() % 16 == 0
+
+
 def segment_gather(x, out_rows, src, ptr=None, fixed_len=0, src_div=1, w_index=None, w=None,
-                   src_scale=None, seg_scale=None, out=None, accumulate=False):
-    """out[s] = seg_scale[s] * sum_{e in seg(s)} w_e * x[src[e] // src_div]  (see dgmc_b200.h)."""
+                   src_scale=None, seg_scale=None, out=None, accumulate=False, blocks=None):
+    """out[s] = seg_scale[s] * sum_{e in seg(s)} w_e * x[src[e] // src_div]  (see dgmc_b200.h).
+    With `blocks` (from csr_blocks) and float4-aligned rows the load-balanced kernel is used."""
     assert x.dim() == 2 and x.stride(1) == 1
     r = x.size(1)
     if out is None:
@@ -45,6 +62,13 @@ def segment_gather(x, out_rows, src, ptr=None, fixed_len=0, src_div=1, w_index=N
         accumulate = False
     assert out.stride(1) == 1 and out.size(0) == out_rows
     if out_rows == 0:
+        return out
+    if ptr is not None and blocks is not None and _vec_ok(x) and _vec_ok(out):
+        nnz = src.numel()
+        ws = _workspace(query('dgmc_balanced_workspace', nnz, r), x.device)
+        call('dgmc_segment_gather_balanced', ptr, blocks, src, int(src_div), w_index, w, src_scale,
+             seg_scale, RowStrided(x), x.stride(0), RowStrided(out), out.stride(0), out_rows, nnz, r,
+             int(bool(accumulate)), ws, ws.numel(), stream_ptr())
         return out
     call('dgmc_segment_gather', ptr, int(fixed_len), src, int(src_div), w_index, w, src_scale,
          seg_scale, RowStrided(x), x.stride(0), RowStrided(out), out.stride(0), out_rows, r,
@@ -69,6 +93,8 @@ class GraphCSR(object):
         self.out_ptr, self.out_edge = csr_build(src, num_nodes)
         self.in_nbr = src[self.in_edge.long()].contiguous()
         self.out_nbr = dst[self.out_edge.long()].contiguous()
+        self.in_blocks = csr_blocks(self.in_ptr, num_nodes, self.num_edges)
+        self.out_blocks = csr_blocks(self.out_ptr, num_nodes, self.num_edges)
         deg_in = (self.in_ptr[1:] - self.in_ptr[:-1]).clamp_(min=1).to(torch.float32)
         deg_out = (self.out_ptr[1:] - self.out_ptr[:-1]).clamp_(min=1).to(torch.float32)
         self.inv_in, self.inv_out = deg_in.reciprocal_(), deg_out.reciprocal_()
@@ -146,7 +172,8 @@ class Candidates(object):
     @property
     def csr(self):
         if self._csr is None:
-            self._csr = csr_build(self.idx.view(-1), self.targets)
+            tptr, perm = csr_build(self.idx.view(-1), self.targets)
+            self._csr = (tptr, perm, csr_blocks(tptr, self.targets, perm.numel()))
         return self._csr
 
 
@@ -227,9 +254,9 @@ class _GatherDot(torch.autograd.Function):
         if ctx.needs_input_grad[0]:  # da[m] = sum_j g[m,j] b[idx[m,j]]
             da = segment_gather(b, cand.m, cand.idx.view(-1), fixed_len=cand.k, w=g.view(-1))
         if ctx.needs_input_grad[1]:  # db[t] = sum_{e -> t} g[e] a[e // k]   (by-target CSR)
-            tptr, perm = cand.csr
+            tptr, perm, blocks = cand.csr
             db = segment_gather(a, cand.targets, perm, ptr=tptr, src_div=cand.k, w_index=perm,
-                                w=g.view(-1))
+                                w=g.view(-1), blocks=blocks)
         return da, db, None
 
 
@@ -245,11 +272,11 @@ class _Transport(torch.autograd.Function):
     @staticmethod
     def forward(ctx, S, r_s, cand):
         S, r_s = _f32(S), _f32(r_s)
-        tptr, perm = cand.csr
+        tptr, perm, blocks = cand.csr
         ctx.cand = cand
         ctx.save_for_backward(S, r_s)
         return segment_gather(r_s, cand.targets, perm, ptr=tptr, src_div=cand.k, w_index=perm,
-                              w=S.view(-1))
+                              w=S.view(-1), blocks=blocks)
 
     @staticmethod
     def backward(ctx, g):
@@ -294,10 +321,11 @@ class _DiffMLP(torch.autograd.Function):
         ws = _workspace(query('dgmc_diff_mlp_bwd_workspace', cand.m, r), g.device)
         call('dgmc_diff_mlp_bwd_rows', g, ps, pt, cand.idx, w2, d_ps, d_w2, d_b2, cand.m, cand.k, r,
              ws, ws.numel(), stream_ptr())
-        tptr, perm = cand.csr
+        tptr, perm, blocks = cand.csr
         d_pt = torch.empty_like(pt)
-        call('dgmc_diff_mlp_bwd_targets', g, ps, pt, tptr, perm, w2, d_pt, cand.targets, cand.k, r,
-             stream_ptr())
+        ws2 = _workspace(query('dgmc_balanced_workspace', perm.numel(), r), g.device)
+        call('dgmc_diff_mlp_bwd_targets_balanced', g, ps, pt, tptr, blocks, perm, w2, d_pt,
+             cand.targets, perm.numel(), cand.k, r, ws2, ws2.numel(), stream_ptr())
         return g, d_ps, d_pt, d_w2, d_b2, None
 
 
@@ -318,9 +346,9 @@ class _RelAggregate(torch.autograd.Function):
         cat = torch.empty(n, 3 * c, dtype=torch.float32, device=x.device)
         cat[:, :c] = x
         segment_gather(x, n, graph.in_nbr, ptr=graph.in_ptr, seg_scale=graph.inv_in,
-                       out=cat[:, c:2 * c])
+                       out=cat[:, c:2 * c], blocks=graph.in_blocks)
         segment_gather(x, n, graph.out_nbr, ptr=graph.out_ptr, seg_scale=graph.inv_out,
-                       out=cat[:, 2 * c:])
+                       out=cat[:, 2 * c:], blocks=graph.out_blocks)
         ctx.graph, ctx.c = graph, c
         return cat
 
@@ -332,10 +360,10 @@ class _RelAggregate(torch.autograd.Function):
         dx = g[:, :c].contiguous()
         # transpose of mean-in: dx[j] += sum_{e: j -> i} inv_in[i] g_in[i]
         segment_gather(g[:, c:2 * c], n, graph.out_nbr, ptr=graph.out_ptr, src_scale=graph.inv_in,
-                       out=dx, accumulate=True)
+                       out=dx, accumulate=True, blocks=graph.out_blocks)
         # transpose of mean-out: dx[j] += sum_{e: i -> j} inv_out[i] g_out[i]
         segment_gather(g[:, 2 * c:], n, graph.in_nbr, ptr=graph.in_ptr, src_scale=graph.inv_out,
-                       out=dx, accumulate=True)
+                       out=dx, accumulate=True, blocks=graph.in_blocks)
         return dx, None
 
 
@@ -350,13 +378,14 @@ class _NeighborSum(torch.autograd.Function):
     def forward(ctx, x, graph):
         ctx.graph = graph
         x = _f32(x)
-        return segment_gather(x, x.size(0), graph.in_nbr, ptr=graph.in_ptr)
+        return segment_gather(x, x.size(0), graph.in_nbr, ptr=graph.in_ptr, blocks=graph.in_blocks)
 
     @staticmethod
     def backward(ctx, g):
         graph = ctx.graph
         g = _f32(g)
-        return segment_gather(g, g.size(0), graph.out_nbr, ptr=graph.out_ptr), None
+        return segment_gather(g, g.size(0), graph.out_nbr, ptr=graph.out_ptr,
+                              blocks=graph.out_blocks), None
 
 
 def neighbor_sum(x, graph):

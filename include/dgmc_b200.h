@@ -105,6 +105,28 @@ int dgmc_segment_gather(const int32_t* ptr, int fixed_len, const int32_t* src, i
                         const float* seg_scale, const float* x, int64_t ldx, float* out,
                         int64_t ldo, int64_t n_seg, int r, int accumulate, dgmc_stream_t stream);
 
+/* ---- load-balanced variants for CSRs with hub segments ---------------------------------------
+ * Same results as dgmc_segment_gather (ptr mode) / dgmc_diff_mlp_bwd_targets, but the unit of work
+ * is a block of DGMC_CSR_BLOCK consecutive ENTRIES rather than a segment, so a target node that sits
+ * in thousands of candidate lists no longer serialises one lane group.  block_seg[b] = segment of
+ * entry b * DGMC_CSR_BLOCK (dgmc_csr_blocks, once per CSR).  Needs r % 4 == 0 and 16-byte aligned
+ * rows; workspace from dgmc_balanced_workspace(nnz, r).  Deterministic (ordered partial sums). */
+#define DGMC_CSR_BLOCK 32
+int dgmc_csr_blocks(const int32_t* ptr, int64_t n_seg, int64_t nnz, int32_t* block_seg,
+                    dgmc_stream_t stream);
+size_t dgmc_balanced_workspace(int64_t nnz, int r);
+int dgmc_segment_gather_balanced(const int32_t* ptr, const int32_t* block_seg, const int32_t* src,
+                                 int src_div, const int32_t* w_index, const float* w,
+                                 const float* src_scale, const float* seg_scale, const float* x,
+                                 int64_t ldx, float* out, int64_t ldo, int64_t n_seg, int64_t nnz, int r,
+                                 int accumulate, void* workspace, size_t workspace_bytes,
+                                 dgmc_stream_t stream);
+int dgmc_diff_mlp_bwd_targets_balanced(const float* g, const float* ps, const float* pt,
+                                       const int32_t* tptr, const int32_t* block_seg,
+                                       const int32_t* perm, const float* w2, float* d_pt, int64_t n_t,
+                                       int64_t nnz, int k, int r, void* workspace,
+                                       size_t workspace_bytes, dgmc_stream_t stream);
+
 /* ---- K6: difference gather + consensus MLP update (hoisted first layer) -----------------
  * s_out[m, j] = s_in[m, j] + b2 + sum_c w2[c] * relu(ps[m, c] - pt[idx[m, j], c])
  * with ps = o_s W1^T + b1 and pt = o_t W1^T computed per NODE by the host (library GEMM):

@@ -275,3 +275,47 @@ def test_topk_simt_exact(B, ns, nt, c, k):
         assert bool(same[safe].all())
     assert torch.allclose(score.double(), picked, rtol=1e-5, atol=1e-5)
     assert bool((score[..., :-1] >= score[..., 1:]).all())  # descending
+
+
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize('r', [8, 64, 128])
+def test_balanced_kernels_with_hub_targets(r):
+    """Half of all candidates point at one hub target, many targets are empty: the entry-parallel
+    kernels must agree with the one-group-per-segment kernels and with scatter_add."""
+    from dgmc import native, ops
+    g = _gen(r)
+    ns, nt, k = 700, 300, 13
+    idx = torch.randint(nt // 2, (1, ns, k), generator=g)
+    idx[0, :, ::2] = 7  # the hub
+    idx = idx.to(DEV)
+    cand = ops.Candidates(idx, nt)
+    tptr, perm, blocks = cand.csr
+    S = torch.rand(ns, k, generator=g).to(DEV)
+    r_s = _randn(g, ns, r)
+    plain = torch.empty(nt, r, device=DEV)
+    native.call('dgmc_segment_gather', tptr, 0, perm, k, perm, S, None, None, r_s, r, plain, r, nt, r, 0,
+                native.stream_ptr())
+    bal = ops.segment_gather(r_s, nt, perm, ptr=tptr, src_div=k, w_index=perm, w=S.view(-1), blocks=blocks)
+    ref = torch.zeros(nt, r, dtype=torch.double, device=DEV).index_add_(
+        0, idx.view(-1), (r_s.double().unsqueeze(1) * S.double().unsqueeze(2)).view(-1, r))
+    assert torch.allclose(bal.double(), ref, rtol=1e-5, atol=1e-4)
+    # the one-group-per-segment kernel adds the hub's ~4,500 terms into ONE fp32 accumulator, the
+    # balanced one in blocks of 32: they differ by fp32 summation order only
+    assert torch.allclose(bal, plain, rtol=1e-4, atol=2e-3)
+    assert torch.equal(bal, ops.segment_gather(r_s, nt, perm, ptr=tptr, src_div=k, w_index=perm,
+                                               w=S.view(-1), blocks=blocks))  # deterministic
+    # accumulate into a strided column slice
+    wide = torch.ones(nt, 3 * r, device=DEV)
+    ops.segment_gather(r_s, nt, perm, ptr=tptr, src_div=k, w_index=perm, w=S.view(-1), blocks=blocks,
+                       out=wide[:, r:2 * r], accumulate=True)
+    assert torch.allclose(wide[:, r:2 * r].double(), ref + 1, rtol=1e-5, atol=1e-4)
+    assert bool((wide[:, :r] == 1).all()) and bool((wide[:, 2 * r:] == 1).all())
+    # K6 backward, target side: both entry points
+    grad, ps, pt, w2 = _randn(g, ns, k), _randn(g, ns, r), _randn(g, nt, r), _randn(g, r)
+    a, b = torch.empty(nt, r, device=DEV), torch.empty(nt, r, device=DEV)
+    native.call('dgmc_diff_mlp_bwd_targets', grad, ps, pt, tptr, perm, w2, a, nt, k, r, native.stream_ptr())
+    ws = torch.empty(native.query('dgmc_balanced_workspace', perm.numel(), r), dtype=torch.uint8, device=DEV)
+    native.call('dgmc_diff_mlp_bwd_targets_balanced', grad, ps, pt, tptr, blocks, perm, w2, b, nt,
+                perm.numel(), k, r, ws, ws.numel(), native.stream_ptr())
+    scale = a.abs().max().item()
+    assert (a - b).abs().max().item() <= 2e-5 * scale + 1e-6
