@@ -3,11 +3,14 @@
 // The by-target CSR of the candidate lists has hub segments: with freshly initialised embeddings a
 // few target nodes sit in thousands of top-k lists, and a kernel that gives one lane group per
 // SEGMENT then waits ~340 us on the longest one (ncu, profiles/README.md r1c).  Here the unit of
-// work is a block of DGMC_CSR_BLOCK consecutive ENTRIES instead: a lane group walks its 32 entries,
-// switching segment as it crosses boundaries.  A segment that lies inside one block is written
-// straight to the output; pieces of a segment that spans several blocks go to a small partial
-// buffer (at most two pieces per block: one that starts at the block start, one that runs to the
-// block end) and a second kernel adds them up in order — still deterministic, no atomics.
+// work is a block of DGMC_CSR_BLOCK = 32 consecutive ENTRIES: a group of G lanes first prefetches
+// the block's metadata (segment id, source row, weight of every entry: 32/G coalesced loads per
+// lane, nothing dependent on a previous gather), then streams the 32 source rows four at a time,
+// switching accumulator whenever the segment id changes.  Control flow is the same for every group
+// of a warp (8 batches), so groups do not serialise each other.  A segment that lies inside one
+// block is written straight to the output; pieces of a segment that spans several blocks go to a
+// small partial buffer (at most two pieces per block: one that starts at the block start, one that
+// runs to the block end) and a second kernel adds them up in order — deterministic, no atomics.
 //
 //   MODE 0: out[s]  = seg_scale[s] * sum_e w_e * x[row_e]                (K4 transport, K5 aggregation)
 //   MODE 1: d_pt[t] = -w2 (.) sum_e g[perm[e]] * [ps[perm[e]/k] > pt[t]]  (K6 backward, target side)
@@ -19,7 +22,7 @@ namespace dgmc {
 constexpr int CB = DGMC_CSR_BLOCK;
 
 struct BalArgs {
-    const int* ptr; const int* block_seg; long long n_seg, nnz;
+    const int* ptr; const int* seg_of; long long n_seg, nnz;
     // MODE 0
     const int* src; int src_div; const int* w_index; const float* w; const float* src_scale;
     const float* seg_scale; const float* x; long long ldx;
@@ -29,24 +32,11 @@ struct BalArgs {
     float* out; long long ldo; int r4; int accumulate; float* partial;
 };
 
-__global__ void __launch_bounds__(256) csr_blocks_kernel(const int* __restrict__ ptr, long long n_seg,
-                                                         long long nnz, int* __restrict__ block_seg) {
-    const long long nblk = (nnz + CB - 1) / CB;
-    const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x; b < nblk; b += stride) {
-        const long long e = b * CB;  // find s with ptr[s] <= e < ptr[s+1]
-        long long lo = 0, hi = n_seg;
-        while (hi - lo > 1) {
-            const long long mid = (lo + hi) >> 1;
-            if (__ldg(ptr + mid) <= e) lo = mid; else hi = mid;
-        }
-        block_seg[b] = (int)lo;
-    }
-}
-
 template <int G, int NV, int MODE>
 __global__ void __launch_bounds__(256) balanced_main_kernel(const BalArgs a) {
-    const int gl = threadIdx.x % G;
+    constexpr int PER = CB / G;  // metadata entries held per lane
+    const int lane = threadIdx.x & 31, gl = lane % G;
+    const unsigned gmask = G == 32 ? 0xffffffffu : (((1u << G) - 1u) << (lane - gl));
     const long long groups = (long long)gridDim.x * (blockDim.x / G);
     const long long nblk = (a.nnz + CB - 1) / CB;
     const int r = a.r4 * 4;
@@ -60,25 +50,52 @@ __global__ void __launch_bounds__(256) balanced_main_kernel(const BalArgs a) {
     }
     for (long long b = (long long)blockIdx.x * (blockDim.x / G) + threadIdx.x / G; b < nblk; b += groups) {
         const long long e_begin = b * CB;
-        const long long e_end = e_begin + CB < a.nnz ? e_begin + CB : a.nnz;
-        long long s = __ldg(a.block_seg + b);
-        long long seg_begin = __ldg(a.ptr + s), seg_end = __ldg(a.ptr + s + 1);
-        long long piece = e_begin, e = e_begin;
+        const int count = (int)(a.nnz - e_begin < CB ? a.nnz - e_begin : CB);
+        // ---- prefetch the block's metadata ---------------------------------------------------
+        int m_seg[PER], m_row[PER]; float m_w[PER];
+#pragma unroll
+        for (int p = 0; p < PER; ++p) {
+            const int j = gl + p * G;
+            const long long e = e_begin + j;
+            int sg = -1, row = 0; float we = 0.f;
+            if (j < count) {
+                sg = __ldg(a.seg_of + e);
+                if (MODE == 0) {
+                    const int sv = __ldg(a.src + e);
+                    row = a.src_div > 1 ? sv / a.src_div : sv;
+                    we = a.w ? __ldg(a.w + (a.w_index ? __ldg(a.w_index + e) : (int)e)) : 1.f;
+                    if (a.src_scale) we *= __ldg(a.src_scale + row);
+                } else {
+                    const int qe = __ldg(a.perm + e);
+                    row = qe / a.k;
+                    we = __ldg(a.g + qe);
+                }
+            }
+            m_seg[p] = sg; m_row[p] = row; m_w[p] = we;
+        }
+        // does the first / last segment of this block continue into the neighbouring blocks?
+        const int first_seg = __shfl_sync(gmask, m_seg[0], lane - gl);
+        const int before = e_begin > 0 ? __ldg(a.seg_of + e_begin - 1) : -1;
+        const int after = e_begin + count < a.nnz ? __ldg(a.seg_of + e_begin + count) : -1;
+
         float4 acc[NV], tv[NV];
 #pragma unroll
-        for (int v = 0; v < NV; ++v) acc[v] = make_float4(0, 0, 0, 0);
-        auto load_own = [&]() {
+        for (int v = 0; v < NV; ++v) { acc[v] = make_float4(0, 0, 0, 0); tv[v] = make_float4(0, 0, 0, 0); }
+        int cur = first_seg;
+        bool at_block_start = true;
+        auto load_own = [&](int s) {
             if (MODE == 1) {
 #pragma unroll
                 for (int v = 0; v < NV; ++v) {
                     const int q = gl + v * G;
-                    tv[v] = q < a.r4 ? ldg4(a.pt + (size_t)s * r + 4 * q) : make_float4(0, 0, 0, 0);
+                    if (q < a.r4) tv[v] = ldg4(a.pt + (size_t)s * r + 4 * q);
                 }
             }
         };
-        auto flush = [&](long long p0, long long p1) {
-            if (p0 >= p1) return;
-            const bool complete = p0 == seg_begin && p1 == seg_end;
+        auto flush = [&](int s, bool ends_at_block_end) {
+            const bool open_left = at_block_start && s == before;
+            const bool open_right = ends_at_block_end && s == after;
+            const bool complete = !open_left && !open_right;
             float sc = 1.f;
             if (MODE == 0 && complete && a.seg_scale) sc = __ldg(a.seg_scale + s);
 #pragma unroll
@@ -93,72 +110,63 @@ __global__ void __launch_bounds__(256) balanced_main_kernel(const BalArgs a) {
                         if (a.accumulate) { const float4 p = *dst; o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w; }
                         *dst = o;
                     } else {
-                        const long long slot = 2 * b + (p0 == e_begin ? 0 : 1);
+                        const long long slot = 2 * b + (at_block_start ? 0 : 1);
                         *reinterpret_cast<float4*>(a.partial + (size_t)slot * r + 4 * q) = o;
                     }
                 }
             }
         };
-        load_own();
-        while (e < e_end) {
-            while (e >= seg_end) {  // leave finished (or empty) segments
-                flush(piece, e);
-                ++s;
-                seg_begin = seg_end;
-                seg_end = __ldg(a.ptr + s + 1);
-                piece = e;
+        load_own(cur);
+        // ---- stream the rows, four at a time ----------------------------------------------------
 #pragma unroll
-                for (int v = 0; v < NV; ++v) acc[v] = make_float4(0, 0, 0, 0);
-                if (e < seg_end) load_own();
-            }
-            const long long lim = seg_end < e_end ? seg_end : e_end;
-            for (; e < lim; e += 4) {
-                int rows[4]; float wt[4];
+        for (int batch = 0; batch < CB / 4; ++batch) {
+            if (batch * 4 < count) {
+                int sg[4], rows[4]; float wt[4];
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
-                    const bool live = e + u < lim;
-                    int row = 0; float we = 0.f;
-                    if (live) {
-                        if (MODE == 0) {
-                            const int sv = __ldg(a.src + e + u);
-                            row = a.src_div > 1 ? sv / a.src_div : sv;
-                            we = a.w ? __ldg(a.w + (a.w_index ? __ldg(a.w_index + e + u) : (int)(e + u))) : 1.f;
-                            if (a.src_scale) we *= __ldg(a.src_scale + row);
-                        } else {
-                            const int qe = __ldg(a.perm + e + u);
-                            row = qe / a.k;
-                            we = __ldg(a.g + qe);
-                        }
-                    }
-                    rows[u] = row; wt[u] = we;
+                    const int j = batch * 4 + u;          // compile-time after unrolling
+                    const int srcl = (lane - gl) + (j % G);
+                    sg[u] = __shfl_sync(gmask, m_seg[j / G], srcl);
+                    rows[u] = __shfl_sync(gmask, m_row[j / G], srcl);
+                    wt[u] = __shfl_sync(gmask, m_w[j / G], srcl);
                 }
+                float4 t[NV][4];
 #pragma unroll
                 for (int v = 0; v < NV; ++v) {
                     const int q = gl + v * G;
-                    if (q < a.r4) {
-                        float4 t[4];
-                        const float* base = MODE == 0 ? a.x : a.ps;
-                        const long long ld = MODE == 0 ? a.ldx : (long long)r;
+                    const float* base = MODE == 0 ? a.x : a.ps;
+                    const long long ld = MODE == 0 ? a.ldx : (long long)r;
 #pragma unroll
-                        for (int u = 0; u < 4; ++u) t[u] = ldg4(base + (size_t)rows[u] * ld + 4 * q);
+                    for (int u = 0; u < 4; ++u)
+                        t[v][u] = q < a.r4 ? ldg4(base + (size_t)rows[u] * ld + 4 * q) : make_float4(0, 0, 0, 0);
+                }
 #pragma unroll
-                        for (int u = 0; u < 4; ++u) {
-                            if (MODE == 0) {
-                                acc[v].x += wt[u] * t[u].x; acc[v].y += wt[u] * t[u].y;
-                                acc[v].z += wt[u] * t[u].z; acc[v].w += wt[u] * t[u].w;
-                            } else {
-                                acc[v].x += t[u].x > tv[v].x ? wt[u] : 0.f;
-                                acc[v].y += t[u].y > tv[v].y ? wt[u] : 0.f;
-                                acc[v].z += t[u].z > tv[v].z ? wt[u] : 0.f;
-                                acc[v].w += t[u].w > tv[v].w ? wt[u] : 0.f;
-                            }
+                for (int u = 0; u < 4; ++u) {
+                    if (sg[u] < 0) continue;              // beyond the last entry
+                    if (sg[u] != cur) {
+                        flush(cur, false);
+                        cur = sg[u];
+                        at_block_start = false;
+#pragma unroll
+                        for (int v = 0; v < NV; ++v) acc[v] = make_float4(0, 0, 0, 0);
+                        load_own(cur);
+                    }
+#pragma unroll
+                    for (int v = 0; v < NV; ++v) {
+                        if (MODE == 0) {
+                            acc[v].x += wt[u] * t[v][u].x; acc[v].y += wt[u] * t[v][u].y;
+                            acc[v].z += wt[u] * t[v][u].z; acc[v].w += wt[u] * t[v][u].w;
+                        } else {
+                            acc[v].x += t[v][u].x > tv[v].x ? wt[u] : 0.f;
+                            acc[v].y += t[v][u].y > tv[v].y ? wt[u] : 0.f;
+                            acc[v].z += t[v][u].z > tv[v].z ? wt[u] : 0.f;
+                            acc[v].w += t[v][u].w > tv[v].w ? wt[u] : 0.f;
                         }
                     }
                 }
             }
-            e = lim;
         }
-        flush(piece, e_end);
+        flush(cur, true);
     }
 }
 
@@ -234,15 +242,6 @@ static int launch_balanced(const BalArgs& a, cudaStream_t stream) {
 
 using namespace dgmc;
 
-extern "C" int dgmc_csr_blocks(const int32_t* ptr, int64_t n_seg, int64_t nnz, int32_t* block_seg,
-                               dgmc_stream_t stream) {
-    DGMC_REQUIRE(ptr && n_seg >= 1 && nnz >= 0, "csr_blocks: bad arguments");
-    if (nnz == 0) return DGMC_OK;
-    DGMC_REQUIRE(block_seg, "csr_blocks: null output");
-    csr_blocks_kernel<<<wave_grid((nnz + CB - 1) / CB, 256, 8), 256, 0, stream>>>(ptr, n_seg, nnz, block_seg);
-    return check_launch("csr_blocks");
-}
-
 extern "C" size_t dgmc_balanced_workspace(int64_t nnz, int r) {
     const size_t nblk = (size_t)((nnz + CB - 1) / CB);
     return 2 * nblk * (size_t)((r + 3) / 4 * 4) * sizeof(float) + 256;
@@ -261,7 +260,7 @@ static int bal_common(const char* who, int r, const void* out, int64_t ldo, void
     return DGMC_OK;
 }
 
-extern "C" int dgmc_segment_gather_balanced(const int32_t* ptr, const int32_t* block_seg, const int32_t* src,
+extern "C" int dgmc_segment_gather_balanced(const int32_t* ptr, const int32_t* seg_of, const int32_t* src,
                                             int src_div, const int32_t* w_index, const float* w,
                                             const float* src_scale, const float* seg_scale, const float* x,
                                             int64_t ldx, float* out, int64_t ldo, int64_t n_seg, int64_t nnz,
@@ -269,7 +268,7 @@ extern "C" int dgmc_segment_gather_balanced(const int32_t* ptr, const int32_t* b
                                             dgmc_stream_t stream) {
     DGMC_REQUIRE(ptr && x && out && n_seg >= 0 && nnz >= 0 && src_div >= 1 && ldx >= r && ldo >= r,
                  "segment_gather_balanced: bad arguments");
-    DGMC_REQUIRE(nnz == 0 || (block_seg && src), "segment_gather_balanced: null CSR arrays");
+    DGMC_REQUIRE(nnz == 0 || (seg_of && src), "segment_gather_balanced: null CSR arrays");
     if (n_seg == 0) return DGMC_OK;
     if (int e = bal_common("segment_gather_balanced", r, out, ldo, workspace, workspace_bytes, nnz)) return e;
     if (ldx % 4 != 0 || (reinterpret_cast<uintptr_t>(x) & 15)) {
@@ -277,7 +276,7 @@ extern "C" int dgmc_segment_gather_balanced(const int32_t* ptr, const int32_t* b
         return DGMC_ERR_UNSUPPORTED;
     }
     BalArgs a{};
-    a.ptr = ptr; a.block_seg = block_seg; a.n_seg = n_seg; a.nnz = nnz;
+    a.ptr = ptr; a.seg_of = seg_of; a.n_seg = n_seg; a.nnz = nnz;
     a.src = src; a.src_div = src_div; a.w_index = w_index; a.w = w; a.src_scale = src_scale;
     a.seg_scale = seg_scale; a.x = x; a.ldx = ldx;
     a.out = out; a.ldo = ldo; a.r4 = r / 4; a.accumulate = accumulate; a.partial = (float*)workspace;
@@ -285,17 +284,17 @@ extern "C" int dgmc_segment_gather_balanced(const int32_t* ptr, const int32_t* b
 }
 
 extern "C" int dgmc_diff_mlp_bwd_targets_balanced(const float* g, const float* ps, const float* pt,
-                                                  const int32_t* tptr, const int32_t* block_seg,
+                                                  const int32_t* tptr, const int32_t* seg_of,
                                                   const int32_t* perm, const float* w2, float* d_pt,
                                                   int64_t n_t, int64_t nnz, int k, int r, void* workspace,
                                                   size_t workspace_bytes, dgmc_stream_t stream) {
     DGMC_REQUIRE(g && ps && pt && tptr && w2 && d_pt && n_t >= 0 && nnz >= 0 && k >= 1,
                  "diff_mlp_bwd_targets_balanced: bad arguments");
-    DGMC_REQUIRE(nnz == 0 || (block_seg && perm), "diff_mlp_bwd_targets_balanced: null CSR arrays");
+    DGMC_REQUIRE(nnz == 0 || (seg_of && perm), "diff_mlp_bwd_targets_balanced: null CSR arrays");
     if (n_t == 0) return DGMC_OK;
     if (int e = bal_common("diff_mlp_bwd_targets_balanced", r, d_pt, r, workspace, workspace_bytes, nnz)) return e;
     BalArgs a{};
-    a.ptr = tptr; a.block_seg = block_seg; a.n_seg = n_t; a.nnz = nnz;
+    a.ptr = tptr; a.seg_of = seg_of; a.n_seg = n_t; a.nnz = nnz;
     a.g = g; a.ps = ps; a.pt = pt; a.perm = perm; a.w2 = w2; a.k = k;
     a.out = d_pt; a.ldo = r; a.r4 = r / 4; a.accumulate = 0; a.partial = (float*)workspace;
     return launch_balanced<1>(a, stream);

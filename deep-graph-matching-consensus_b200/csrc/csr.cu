@@ -205,8 +205,8 @@ extern "C" size_t dgmc_csr_build_workspace(int64_t nnz, int64_t n_seg) {
 }
 
 extern "C" int dgmc_csr_build(const int32_t* keys, int64_t nnz, int64_t n_seg, int32_t* ptr,
-                              int32_t* perm, void* workspace, size_t workspace_bytes,
-                              dgmc_stream_t stream) {
+                              int32_t* perm, int32_t* sorted_keys, void* workspace,
+                              size_t workspace_bytes, dgmc_stream_t stream) {
     DGMC_REQUIRE(ptr && nnz >= 0 && n_seg >= 0 && nnz < (1ll << 31) && n_seg < (1ll << 31) - 1,
                  "csr_build: bad sizes (nnz=%lld n_seg=%lld)", (long long)nnz, (long long)n_seg);
     DGMC_REQUIRE(nnz == 0 || (keys && perm && workspace), "csr_build: null pointer");
@@ -237,10 +237,9 @@ extern "C" int dgmc_csr_build(const int32_t* keys, int64_t nnz, int64_t n_seg, i
     const int* src_v = nullptr;
     for (int pass = 0; pass < passes; ++pass) {
         const bool last = pass == passes - 1;
-        int* dst_k = (pass & 1) ? k1 : k0;
+        int* dst_k = (last && sorted_keys) ? sorted_keys : ((pass & 1) ? k1 : k0);
         // payload alternates perm <-> v1, arranged so that the final write lands in perm
         int* dst_v = ((passes - 1 - pass) & 1) ? v1 : perm;
-        (void)last;
         radix_hist_kernel<<<(int)p.tiles, RS_THREADS, 0, stream>>>(src_k, nnz, 8 * pass, table,
                                                                    (int)p.tiles);
         scan_tiles_kernel<<<(int)p.scan_tiles, 1024, 0, stream>>>(table, table, p.table, sums);

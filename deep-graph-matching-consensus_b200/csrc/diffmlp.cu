@@ -152,14 +152,17 @@ __global__ void __launch_bounds__(256) diff_mlp_bwd_rows_kernel(
     }
 }
 
+// one warp per output column: lanes stride over the per-block partials, fixed shuffle tree
 __global__ void __launch_bounds__(256) diff_mlp_bwd_finish_kernel(const float* __restrict__ partial,
                                                                   int blocks, int r,
                                                                   float* __restrict__ d_w2,
                                                                   float* __restrict__ d_b2) {
-    for (int c = blockIdx.x * blockDim.x + threadIdx.x; c <= r; c += gridDim.x * blockDim.x) {
+    const int lane = threadIdx.x & 31;
+    for (int c = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); c <= r; c += gridDim.x * (blockDim.x >> 5)) {
         float s = 0.f;
-        for (int b = 0; b < blocks; ++b) s += partial[(size_t)b * (r + 1) + c];
-        if (c < r) d_w2[c] = s; else *d_b2 = s;
+        for (int b = lane; b < blocks; b += 32) s += partial[(size_t)b * (r + 1) + c];
+        s = warp_sum(s);
+        if (lane == 0) { if (c < r) d_w2[c] = s; else *d_b2 = s; }
     }
 }
 
@@ -274,7 +277,7 @@ extern "C" int dgmc_diff_mlp_bwd_rows(const float* g, const float* ps, const flo
     const size_t smem = 8 * (size_t)(r + 1) * sizeof(float);
     float* partial = (float*)workspace;
     DM_DISPATCH(diff_mlp_bwd_rows_kernel, grid, smem, g, ps, pt, idx, w2, d_ps, partial, m, k, r4);
-    diff_mlp_bwd_finish_kernel<<<(r + 256) / 256, 256, 0, stream>>>(partial, grid, r, d_w2, d_b2);
+    diff_mlp_bwd_finish_kernel<<<(r + 8) / 8, 256, 0, stream>>>(partial, grid, r, d_w2, d_b2);
     return check_launch("diff_mlp_bwd_rows", 2);
 }
 

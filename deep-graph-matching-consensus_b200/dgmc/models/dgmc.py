@@ -148,13 +148,13 @@ class DGMC(torch.nn.Module):
                 # psi_2 shares its weights between the two graphs: run it ONCE on their disjoint
                 # union (same arithmetic per node, half the launches, twice the GEMM height)
                 o = self.psi_2(torch.cat([r_s, r_t], dim=0), merged.edge_index, merged.edge_attr)
-                p = o @ w1.t()
+                p = ops.node_linear(o, w1)
                 p_s, p_t = p[:r_s.size(0)] + b1, p[r_s.size(0):]
                 return _repad(p_s, s_mask), _repad(p_t, t_mask)
             o_s = self.psi_2(r_s, edge_index_s, edge_attr_s)
             o_t = self.psi_2(r_t, edge_index_t, edge_attr_t)
             o_s, o_t = _repad(o_s, s_mask), _repad(o_t, t_mask)
-            return torch.addmm(b1, o_s, w1.t()), o_t @ w1.t()
+            return ops.node_linear(o_s, w1, b1), ops.node_linear(o_t, w1)
 
         if self.k < 1:
             # ------ dense variant (dgmc.py:161-183) ------

@@ -23,28 +23,18 @@ def _workspace(nbytes, device):
 # --------------------------------------------------------------------------------------------
 # CSR helpers
 # --------------------------------------------------------------------------------------------
-def csr_build(keys, n_seg):
-    """keys int32 [nnz] in [0, n_seg) -> (ptr int32 [n_seg + 1], perm int32 [nnz]), stable."""
+def csr_build(keys, n_seg, want_sorted=False):
+    """keys int32 [nnz] in [0, n_seg) -> (ptr int32 [n_seg + 1], perm int32 [nnz]) — a stable sort;
+    with want_sorted also keys[perm] (the segment id of every CSR slot, used by the balanced kernels)."""
     keys = keys.contiguous()
     assert keys.dtype == torch.int32
     nnz = keys.numel()
     ptr = torch.empty(n_seg + 1, dtype=torch.int32, device=keys.device)
     perm = torch.empty(nnz, dtype=torch.int32, device=keys.device)
+    seg_of = torch.empty(max(nnz, 1), dtype=torch.int32, device=keys.device) if want_sorted else None
     ws = _workspace(query('dgmc_csr_build_workspace', nnz, n_seg), keys.device)
-    call('dgmc_csr_build', keys, nnz, n_seg, ptr, perm, ws, ws.numel(), stream_ptr())
-    return ptr, perm
-
-
-def csr_blocks(ptr, n_seg, nnz):
-    """block_seg[b] = segment of entry b * DGMC_CSR_BLOCK (work list of the balanced kernels)."""
-    nblk = (nnz + CSR_BLOCK - 1) // CSR_BLOCK
-    blocks = torch.empty(max(nblk, 1), dtype=torch.int32, device=ptr.device)
-    if nnz > 0:
-        call('dgmc_csr_blocks', ptr, n_seg, nnz, blocks, stream_ptr())
-    return blocks
-
-
-CSR_BLOCK = 32  # DGMC_CSR_BLOCK in include/dgmc_b200.h
+    call('dgmc_csr_build', keys, nnz, n_seg, ptr, perm, seg_of, ws, ws.numel(), stream_ptr())
+    return (ptr, perm, seg_of) if want_sorted else (ptr, perm)
 
 
 def _vec_ok(t):
@@ -52,9 +42,9 @@ def _vec_ok(t):
 
 
 def segment_gather(x, out_rows, src, ptr=None, fixed_len=0, src_div=1, w_index=None, w=None,
-                   src_scale=None, seg_scale=None, out=None, accumulate=False, blocks=None):
+                   src_scale=None, seg_scale=None, out=None, accumulate=False, seg_of=None):
     """out[s] = seg_scale[s] * sum_{e in seg(s)} w_e * x[src[e] // src_div]  (see dgmc_b200.h).
-    With `blocks` (from csr_blocks) and float4-aligned rows the load-balanced kernel is used."""
+    With `seg_of` (csr_build(..., want_sorted=True)) and float4-aligned rows the load-balanced kernel is used."""
     assert x.dim() == 2 and x.stride(1) == 1
     r = x.size(1)
     if out is None:
@@ -63,10 +53,10 @@ def segment_gather(x, out_rows, src, ptr=None, fixed_len=0, src_div=1, w_index=N
     assert out.stride(1) == 1 and out.size(0) == out_rows
     if out_rows == 0:
         return out
-    if ptr is not None and blocks is not None and _vec_ok(x) and _vec_ok(out):
+    if ptr is not None and seg_of is not None and _vec_ok(x) and _vec_ok(out):
         nnz = src.numel()
         ws = _workspace(query('dgmc_balanced_workspace', nnz, r), x.device)
-        call('dgmc_segment_gather_balanced', ptr, blocks, src, int(src_div), w_index, w, src_scale,
+        call('dgmc_segment_gather_balanced', ptr, seg_of, src, int(src_div), w_index, w, src_scale,
              seg_scale, RowStrided(x), x.stride(0), RowStrided(out), out.stride(0), out_rows, nnz, r,
              int(bool(accumulate)), ws, ws.numel(), stream_ptr())
         return out
@@ -89,12 +79,10 @@ class GraphCSR(object):
         src = edge_index[0].to(torch.int32).contiguous()
         dst = edge_index[1].to(torch.int32).contiguous()
         self.num_nodes, self.num_edges = num_nodes, src.numel()
-        self.in_ptr, self.in_edge = csr_build(dst, num_nodes)
-        self.out_ptr, self.out_edge = csr_build(src, num_nodes)
+        self.in_ptr, self.in_edge, self.in_seg = csr_build(dst, num_nodes, True)
+        self.out_ptr, self.out_edge, self.out_seg = csr_build(src, num_nodes, True)
         self.in_nbr = src[self.in_edge.long()].contiguous()
         self.out_nbr = dst[self.out_edge.long()].contiguous()
-        self.in_blocks = csr_blocks(self.in_ptr, num_nodes, self.num_edges)
-        self.out_blocks = csr_blocks(self.out_ptr, num_nodes, self.num_edges)
         deg_in = (self.in_ptr[1:] - self.in_ptr[:-1]).clamp_(min=1).to(torch.float32)
         deg_out = (self.out_ptr[1:] - self.out_ptr[:-1]).clamp_(min=1).to(torch.float32)
         self.inv_in, self.inv_out = deg_in.reciprocal_(), deg_out.reciprocal_()
@@ -172,8 +160,7 @@ class Candidates(object):
     @property
     def csr(self):
         if self._csr is None:
-            tptr, perm = csr_build(self.idx.view(-1), self.targets)
-            self._csr = (tptr, perm, csr_blocks(tptr, self.targets, perm.numel()))
+            self._csr = csr_build(self.idx.view(-1), self.targets, True)
         return self._csr
 
 
@@ -254,9 +241,9 @@ class _GatherDot(torch.autograd.Function):
         if ctx.needs_input_grad[0]:  # da[m] = sum_j g[m,j] b[idx[m,j]]
             da = segment_gather(b, cand.m, cand.idx.view(-1), fixed_len=cand.k, w=g.view(-1))
         if ctx.needs_input_grad[1]:  # db[t] = sum_{e -> t} g[e] a[e // k]   (by-target CSR)
-            tptr, perm, blocks = cand.csr
+            tptr, perm, seg_of = cand.csr
             db = segment_gather(a, cand.targets, perm, ptr=tptr, src_div=cand.k, w_index=perm,
-                                w=g.view(-1), blocks=blocks)
+                                w=g.view(-1), seg_of=seg_of)
         return da, db, None
 
 
@@ -272,11 +259,11 @@ class _Transport(torch.autograd.Function):
     @staticmethod
     def forward(ctx, S, r_s, cand):
         S, r_s = _f32(S), _f32(r_s)
-        tptr, perm, blocks = cand.csr
+        tptr, perm, seg_of = cand.csr
         ctx.cand = cand
         ctx.save_for_backward(S, r_s)
         return segment_gather(r_s, cand.targets, perm, ptr=tptr, src_div=cand.k, w_index=perm,
-                              w=S.view(-1), blocks=blocks)
+                              w=S.view(-1), seg_of=seg_of)
 
     @staticmethod
     def backward(ctx, g):
@@ -321,10 +308,10 @@ class _DiffMLP(torch.autograd.Function):
         ws = _workspace(query('dgmc_diff_mlp_bwd_workspace', cand.m, r), g.device)
         call('dgmc_diff_mlp_bwd_rows', g, ps, pt, cand.idx, w2, d_ps, d_w2, d_b2, cand.m, cand.k, r,
              ws, ws.numel(), stream_ptr())
-        tptr, perm, blocks = cand.csr
+        tptr, perm, seg_of = cand.csr
         d_pt = torch.empty_like(pt)
         ws2 = _workspace(query('dgmc_balanced_workspace', perm.numel(), r), g.device)
-        call('dgmc_diff_mlp_bwd_targets_balanced', g, ps, pt, tptr, blocks, perm, w2, d_pt,
+        call('dgmc_diff_mlp_bwd_targets_balanced', g, ps, pt, tptr, seg_of, perm, w2, d_pt,
              cand.targets, perm.numel(), cand.k, r, ws2, ws2.numel(), stream_ptr())
         return g, d_ps, d_pt, d_w2, d_b2, None
 
@@ -333,6 +320,42 @@ def diff_mlp(s_hat, ps, pt, w2, b2, cand):
     """S_hat + Lin2(ReLU(Lin1(o_s - o_t[S_idx]))) with Lin1 hoisted to the nodes (dgmc.py:219-223).
     ps [M, R4], pt [B*N_t, R4] (R4 = R padded to a multiple of 4), w2 [R4], b2 [1]."""
     return _DiffMLP.apply(s_hat, ps, pt, w2, b2, cand)
+
+
+# --------------------------------------------------------------------------------------------
+# per-node linear map with a split-K weight gradient
+# --------------------------------------------------------------------------------------------
+class _NodeLinear(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias):
+        ctx.save_for_backward(x, weight)
+        ctx.has_bias = bias is not None
+        return torch.addmm(bias, x, weight.t()) if bias is not None else x @ weight.t()
+
+    @staticmethod
+    def backward(ctx, g):
+        x, weight = ctx.saved_tensors
+        g = _f32(g)
+        k, m, n = x.size(0), weight.size(0), weight.size(1)
+        dx = g @ weight if ctx.needs_input_grad[0] else None
+        dw = db = None
+        if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
+            dw = torch.empty_like(weight)
+            db = torch.empty(m, dtype=torch.float32, device=g.device) if ctx.has_bias else None
+            ws = _workspace(query('dgmc_wgrad_workspace', k, m, n), g.device)
+            call('dgmc_wgrad', g, g.stride(0), RowStrided(x), x.stride(0), k, m, n, dw, db, ws,
+                 ws.numel(), stream_ptr())
+        return dx, dw, db
+
+
+def node_linear(x, weight, bias=None):
+    """x [nodes, in] @ weight[out, in]^T (+ bias): library GEMM forward and input gradient; the
+    weight / bias gradient (a reduction over all nodes with a tiny output) runs on the split-K kernel
+    dgmc_wgrad when the output is small, else stays with the library."""
+    if weight.size(0) * weight.size(1) <= 64 * 1024 and x.size(0) >= 2048 and x.is_cuda \
+            and x.dtype == torch.float32 and x.stride(1) == 1:
+        return _NodeLinear.apply(x, weight, bias)
+    return torch.nn.functional.linear(x, weight, bias)
 
 
 # --------------------------------------------------------------------------------------------
@@ -346,9 +369,9 @@ class _RelAggregate(torch.autograd.Function):
         cat = torch.empty(n, 3 * c, dtype=torch.float32, device=x.device)
         cat[:, :c] = x
         segment_gather(x, n, graph.in_nbr, ptr=graph.in_ptr, seg_scale=graph.inv_in,
-                       out=cat[:, c:2 * c], blocks=graph.in_blocks)
+                       out=cat[:, c:2 * c], seg_of=graph.in_seg)
         segment_gather(x, n, graph.out_nbr, ptr=graph.out_ptr, seg_scale=graph.inv_out,
-                       out=cat[:, 2 * c:], blocks=graph.out_blocks)
+                       out=cat[:, 2 * c:], seg_of=graph.out_seg)
         ctx.graph, ctx.c = graph, c
         return cat
 
@@ -360,10 +383,10 @@ class _RelAggregate(torch.autograd.Function):
         dx = g[:, :c].contiguous()
         # transpose of mean-in: dx[j] += sum_{e: j -> i} inv_in[i] g_in[i]
         segment_gather(g[:, c:2 * c], n, graph.out_nbr, ptr=graph.out_ptr, src_scale=graph.inv_in,
-                       out=dx, accumulate=True, blocks=graph.out_blocks)
+                       out=dx, accumulate=True, seg_of=graph.out_seg)
         # transpose of mean-out: dx[j] += sum_{e: i -> j} inv_out[i] g_out[i]
         segment_gather(g[:, 2 * c:], n, graph.in_nbr, ptr=graph.in_ptr, src_scale=graph.inv_out,
-                       out=dx, accumulate=True, blocks=graph.in_blocks)
+                       out=dx, accumulate=True, seg_of=graph.in_seg)
         return dx, None
 
 
@@ -378,14 +401,14 @@ class _NeighborSum(torch.autograd.Function):
     def forward(ctx, x, graph):
         ctx.graph = graph
         x = _f32(x)
-        return segment_gather(x, x.size(0), graph.in_nbr, ptr=graph.in_ptr, blocks=graph.in_blocks)
+        return segment_gather(x, x.size(0), graph.in_nbr, ptr=graph.in_ptr, seg_of=graph.in_seg)
 
     @staticmethod
     def backward(ctx, g):
         graph = ctx.graph
         g = _f32(g)
         return segment_gather(g, g.size(0), graph.out_nbr, ptr=graph.out_ptr,
-                              blocks=graph.out_blocks), None
+                              seg_of=graph.out_seg), None
 
 
 def neighbor_sum(x, graph):

@@ -88,6 +88,7 @@ int dgmc_gather_dot_fwd(const float* a, int64_t lda, const float* b, int64_t ldb
  * once per edge_index and cached by the host. */
 size_t dgmc_csr_build_workspace(int64_t nnz, int64_t n_seg);
 int dgmc_csr_build(const int32_t* keys, int64_t nnz, int64_t n_seg, int32_t* ptr, int32_t* perm,
+                   int32_t* sorted_keys /* nullable: keys[perm], the segment id of every CSR slot */,
                    void* workspace, size_t workspace_bytes, dgmc_stream_t stream);
 
 /* ---- K4 / K5: segmented weighted gather-reduce -----------------------------------------
@@ -109,20 +110,19 @@ int dgmc_segment_gather(const int32_t* ptr, int fixed_len, const int32_t* src, i
  * Same results as dgmc_segment_gather (ptr mode) / dgmc_diff_mlp_bwd_targets, but the unit of work
  * is a block of DGMC_CSR_BLOCK consecutive ENTRIES rather than a segment, so a target node that sits
  * in thousands of candidate lists no longer serialises one lane group.  block_seg[b] = segment of
- * entry b * DGMC_CSR_BLOCK (dgmc_csr_blocks, once per CSR).  Needs r % 4 == 0 and 16-byte aligned
- * rows; workspace from dgmc_balanced_workspace(nnz, r).  Deterministic (ordered partial sums). */
+ * seg_of[e] = segment id of CSR slot e (`sorted_keys` of dgmc_csr_build).  Needs r % 4 == 0 and
+ * 16-byte aligned rows; workspace from dgmc_balanced_workspace(nnz, r).  Deterministic (ordered
+ * partial sums). */
 #define DGMC_CSR_BLOCK 32
-int dgmc_csr_blocks(const int32_t* ptr, int64_t n_seg, int64_t nnz, int32_t* block_seg,
-                    dgmc_stream_t stream);
 size_t dgmc_balanced_workspace(int64_t nnz, int r);
-int dgmc_segment_gather_balanced(const int32_t* ptr, const int32_t* block_seg, const int32_t* src,
+int dgmc_segment_gather_balanced(const int32_t* ptr, const int32_t* seg_of, const int32_t* src,
                                  int src_div, const int32_t* w_index, const float* w,
                                  const float* src_scale, const float* seg_scale, const float* x,
                                  int64_t ldx, float* out, int64_t ldo, int64_t n_seg, int64_t nnz, int r,
                                  int accumulate, void* workspace, size_t workspace_bytes,
                                  dgmc_stream_t stream);
 int dgmc_diff_mlp_bwd_targets_balanced(const float* g, const float* ps, const float* pt,
-                                       const int32_t* tptr, const int32_t* block_seg,
+                                       const int32_t* tptr, const int32_t* seg_of,
                                        const int32_t* perm, const float* w2, float* d_pt, int64_t n_t,
                                        int64_t nnz, int k, int r, void* workspace,
                                        size_t workspace_bytes, dgmc_stream_t stream);
@@ -178,6 +178,15 @@ int dgmc_spline_gather_bwd(const float* g, int64_t ldg, const int32_t* out_ptr,
                            const int32_t* out_nbr, const int32_t* out_edge, const float* basis,
                            const int32_t* widx, int n_corners, const float* inv_deg, float* dy,
                            int64_t n, int n_kernels, int c, dgmc_stream_t stream);
+
+/* ---- weight gradient of a per-node linear map (split-K) -----------------------------------------
+ * dw[m, n] = sum_k g[k, m] * x[k, n];  db[m] = sum_k g[k, m] (db may be NULL).  g [k, m], x [k, n].
+ * replaces the autograd backward of the Linear layers in rel.py:28-31 / :89 and dgmc.py:74-78 when
+ * the node count k is large and m x n is small: a library SGEMM tiles only the 64 x 192 output and
+ * runs on 3 CTAs; this kernel splits the node dimension over the whole chip.  fp32, deterministic. */
+size_t dgmc_wgrad_workspace(int64_t k, int m, int n);
+int dgmc_wgrad(const float* g, int64_t ldg, const float* x, int64_t ldx, int64_t k, int m, int n,
+               float* dw, float* db, void* workspace, size_t workspace_bytes, dgmc_stream_t stream);
 
 /* ---- dense branch: consensus update without materialising D [B, N_s, N_t, R] ----------------
  * s_out[b,i,j] = s_in[b,i,j] + [s_mask[b,i] & t_mask[b,j]] * (b2 + sum_c w2[c] relu(ps[b,i,c] - pt[b,j,c]))

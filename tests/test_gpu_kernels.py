@@ -289,13 +289,13 @@ def test_balanced_kernels_with_hub_targets(r):
     idx[0, :, ::2] = 7  # the hub
     idx = idx.to(DEV)
     cand = ops.Candidates(idx, nt)
-    tptr, perm, blocks = cand.csr
+    tptr, perm, seg_of = cand.csr
     S = torch.rand(ns, k, generator=g).to(DEV)
     r_s = _randn(g, ns, r)
     plain = torch.empty(nt, r, device=DEV)
     native.call('dgmc_segment_gather', tptr, 0, perm, k, perm, S, None, None, r_s, r, plain, r, nt, r, 0,
                 native.stream_ptr())
-    bal = ops.segment_gather(r_s, nt, perm, ptr=tptr, src_div=k, w_index=perm, w=S.view(-1), blocks=blocks)
+    bal = ops.segment_gather(r_s, nt, perm, ptr=tptr, src_div=k, w_index=perm, w=S.view(-1), seg_of=seg_of)
     ref = torch.zeros(nt, r, dtype=torch.double, device=DEV).index_add_(
         0, idx.view(-1), (r_s.double().unsqueeze(1) * S.double().unsqueeze(2)).view(-1, r))
     assert torch.allclose(bal.double(), ref, rtol=1e-5, atol=1e-4)
@@ -303,10 +303,10 @@ def test_balanced_kernels_with_hub_targets(r):
     # balanced one in blocks of 32: they differ by fp32 summation order only
     assert torch.allclose(bal, plain, rtol=1e-4, atol=2e-3)
     assert torch.equal(bal, ops.segment_gather(r_s, nt, perm, ptr=tptr, src_div=k, w_index=perm,
-                                               w=S.view(-1), blocks=blocks))  # deterministic
+                                               w=S.view(-1), seg_of=seg_of))  # deterministic
     # accumulate into a strided column slice
     wide = torch.ones(nt, 3 * r, device=DEV)
-    ops.segment_gather(r_s, nt, perm, ptr=tptr, src_div=k, w_index=perm, w=S.view(-1), blocks=blocks,
+    ops.segment_gather(r_s, nt, perm, ptr=tptr, src_div=k, w_index=perm, w=S.view(-1), seg_of=seg_of,
                        out=wide[:, r:2 * r], accumulate=True)
     assert torch.allclose(wide[:, r:2 * r].double(), ref + 1, rtol=1e-5, atol=1e-4)
     assert bool((wide[:, :r] == 1).all()) and bool((wide[:, 2 * r:] == 1).all())
@@ -315,7 +315,34 @@ def test_balanced_kernels_with_hub_targets(r):
     a, b = torch.empty(nt, r, device=DEV), torch.empty(nt, r, device=DEV)
     native.call('dgmc_diff_mlp_bwd_targets', grad, ps, pt, tptr, perm, w2, a, nt, k, r, native.stream_ptr())
     ws = torch.empty(native.query('dgmc_balanced_workspace', perm.numel(), r), dtype=torch.uint8, device=DEV)
-    native.call('dgmc_diff_mlp_bwd_targets_balanced', grad, ps, pt, tptr, blocks, perm, w2, b, nt,
+    native.call('dgmc_diff_mlp_bwd_targets_balanced', grad, ps, pt, tptr, seg_of, perm, w2, b, nt,
                 perm.numel(), k, r, ws, ws.numel(), native.stream_ptr())
     scale = a.abs().max().item()
     assert (a - b).abs().max().item() <= 2e-5 * scale + 1e-6
+
+
+@pytest.mark.parametrize('k,m,n', [(39000, 64, 192), (5000, 64, 256), (3000, 8, 24), (2500, 33, 70),
+                                   (100000, 64, 64)])
+def test_node_linear_wgrad_matches_autograd(k, m, n):
+    from dgmc import ops
+    g = _gen(k + m + n)
+    x = _randn(g, k, n).requires_grad_()
+    w = (_randn(g, m, n) * 0.1).requires_grad_()
+    b = _randn(g, m).requires_grad_()
+    go = _randn(g, k, m)
+    out = ops.node_linear(x, w, b)
+    out.backward(go)
+    xr, wr, br = [t.detach().double().requires_grad_() for t in (x, w, b)]
+    ref = torch.nn.functional.linear(xr, wr, br)
+    ref.backward(go.double())
+    assert torch.allclose(out.double(), ref, rtol=1e-5, atol=1e-5)
+    for a, r_ in ((x.grad, xr.grad), (w.grad, wr.grad), (b.grad, br.grad)):
+        scale = r_.abs().max().item()
+        assert (a.double() - r_).abs().max().item() <= 2e-5 * scale + 1e-6
+    # strided input (a column slice) and no bias
+    wide = _randn(g, k, n + 8)
+    xs = wide[:, 4:4 + n].detach().requires_grad_()
+    w2 = w.detach().clone().requires_grad_()
+    ops.node_linear(xs, w2).backward(go)
+    ref_w = go.double().t() @ wide[:, 4:4 + n].double()
+    assert (w2.grad.double() - ref_w).abs().max().item() <= 2e-5 * ref_w.abs().max().item() + 1e-6
