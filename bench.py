@@ -26,7 +26,17 @@ for _p in (ROOT, PKG):
     if _p not in sys.path:
         sys.path.insert(0, _p)
 
+# stdout carries exactly ONE JSON line: native libraries (NCCL prints its version banner there)
+# write to file descriptor 1 directly, so point fd 1 at stderr and keep the real stdout aside.
+_REAL_STDOUT = os.fdopen(os.dup(1), 'w')
+os.dup2(2, 1)
+
 import torch  # noqa: E402
+
+
+def emit(obj):
+    _REAL_STDOUT.write(json.dumps(obj) + '\n')
+    _REAL_STDOUT.flush()
 
 WORKLOAD = dict(name='DBP15K zh_en-shaped synthetic pair', n_s=19388, n_t=19572, feat=300,
                 e_s=70414, e_t=95142, dim=256, rnd_dim=64, layers=3, k=10, num_steps=10,
@@ -155,13 +165,14 @@ def cpu_reference_steps(w, inputs, steps, warmup, budget_s):
 # ------------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------------
-def build_model(w, device):
-    from dgmc.models import DGMC, RelCNN
+def build_model(w, device, sharded=False):
+    from dgmc.models import DGMC, RelCNN, RowShardedDGMC
     torch.manual_seed(0)
     psi_1 = RelCNN(w['feat'], w['dim'], w['layers'], batch_norm=False, cat=True, lin=True, dropout=0.5)
     psi_2 = RelCNN(w['rnd_dim'], w['rnd_dim'], w['layers'], batch_norm=False, cat=True, lin=True,
                    dropout=0.0)
-    model = DGMC(psi_1, psi_2, num_steps=w['num_steps'], k=w['k'], detach=True).to(device)
+    cls = RowShardedDGMC if sharded else DGMC
+    model = cls(psi_1, psi_2, num_steps=w['num_steps'], k=w['k'], detach=True).to(device)
     model.train()
     return model
 
@@ -171,6 +182,8 @@ def train_step(model, opt, d):
     _, S_L = model(d['x_s'], d['e_s'], None, None, d['x_t'], d['e_t'], None, None, d['y'])
     loss = model.loss(S_L, d['y'])
     loss.backward()
+    if hasattr(model, 'sync_gradients'):
+        model.sync_gradients()
     opt.step()
     return loss
 
@@ -243,6 +256,11 @@ def kernel_rooflines(w, model, d, peaks, step_ms):
     return rows
 
 
+def stage(msg):
+    if os.environ.get('DGMC_BENCH_VERBOSE'):
+        print('[bench rank %s] %s' % (os.environ.get('RANK', '0'), msg), file=sys.stderr, flush=True)
+
+
 def load_peaks():
     path = os.path.join(ROOT, 'MEASURED_PEAKS.json')
     if os.path.exists(path):
@@ -286,7 +304,7 @@ def main():
         sps, n, cores, dt = cpu_reference_steps(w, inputs, args.steps, args.warmup, budget)
         sample = ('%d full steps of the same workload (oracle port of the reference: torch CPU '
                   'ops, row-chunked matmul+topk for __top_k__), %d threads' % (n, cores))
-        print(json.dumps({
+        emit({
             'impl': 'reference', 'metric': METRIC, 'value': sps, 'unit': 'steps/s', 'n_gpus': 0,
             'steps': n, 'warmup': 1, 'ms_per_step': dt * 1e3, 'higher_is_better': True,
             'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
@@ -294,20 +312,22 @@ def main():
             'cpu_baseline': {'value': sps, 'unit': 'steps/s', 'cores': cores, 'kind': 'port',
                              'sample': sample},
             'e2e': {'value': sps, 'unit': 'steps/s', 'h2d_bytes_per_step': 0,
-                    'd2h_bytes_per_step': 0}}))
+                    'd2h_bytes_per_step': 0}})
         return 0
 
     import torch.distributed as dist
     torch.cuda.set_device(local)
     dev = torch.device('cuda', local)
     if world > 1:
+        os.environ.setdefault('TORCH_NCCL_ASYNC_ERROR_HANDLING', '0')  # collectives get graph-captured
         dist.init_process_group('nccl', device_id=dev)
     from dgmc import native
 
     host = make_inputs(w)
     pinned = {k: v.pin_memory() for k, v in host.items()}
     d = {k: v.to(dev) for k, v in host.items()}
-    model = build_model(w, dev)
+    model = build_model(w, dev, sharded=world > 1)
+    torch.manual_seed(1234)  # every rank draws the same indicator / negative / dropout streams
     opt = torch.optim.Adam([p for p in model.parameters()], lr=1e-3, capturable=True)
 
     def barrier():
@@ -324,12 +344,13 @@ def main():
             train_step(model, opt, d)
         torch.cuda.synchronize()
         torch.cuda.nvtx.range_pop()
-        print(json.dumps({'profile_eager_steps': args.steps}))
+        emit({'profile_eager_steps': args.steps})
         return 0
 
     from dgmc.utils import GraphedTrainStep
     args_of = lambda t: (t['x_s'], t['e_s'], None, None, t['x_t'], t['e_t'], None, None, t['y'])  # noqa: E731
 
+    stage('eager warm-up')
     # ---- eager step (plain Python loop over the public API), for reference ------------------
     for _ in range(args.warmup):
         train_step(model, opt, d)
@@ -346,7 +367,9 @@ def main():
     launches = (native.lib.dgmc_launch_count() - launches0) // n_eager
 
     # ---- resident inputs: the whole step captured in one CUDA graph -------------------------
+    stage('capturing graph (static structure)')
     graphed = GraphedTrainStep(model, opt, *args_of(d), structure_is_static=True)
+    stage('graph captured')
     for _ in range(args.warmup):
         graphed(*args_of(d))
     barrier()
@@ -361,12 +384,14 @@ def main():
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms_per_step = ms.item() / args.steps
-    value = world * 1e3 / ms_per_step  # replicas: every rank runs the whole pair
+    value = 1e3 / ms_per_step  # one job: with N > 1 the source rows are sharded over the ranks
 
     # ---- end-to-end: pinned host inputs copied every step (graph structure rebuilt inside the
     #      captured step), loss read back --------------------------------------------------------
     h2d = sum(v.numel() * v.element_size() for v in pinned.values())
+    stage('capturing e2e graph')
     e2e_step = GraphedTrainStep(model, opt, *args_of(d), structure_is_static=False)
+    stage('e2e graph captured')
     for _ in range(3):
         e2e_step(*args_of(pinned)).item()
     barrier()
@@ -379,8 +404,25 @@ def main():
     ms2 = torch.tensor([start.elapsed_time(end)], device=dev)
     if world > 1:
         dist.all_reduce(ms2, op=dist.ReduceOp.MAX)
-    e2e_value = world * 1e3 / (ms2.item() / args.steps)
+    e2e_value = 1e3 / (ms2.item() / args.steps)
 
+    stage('timing done')
+    if world > 1:  # all collective work is over: leave the group before rank 0's local epilogue
+        dist.barrier()
+        torch.cuda.synchronize()
+        stage('last barrier passed')
+        # Tearing the NCCL communicator down while captured graphs still reference it can block, and
+        # a rank that vanishes early makes the others abort: the helper ranks wait (on the TCP store,
+        # not on NCCL) until rank 0 has printed, then everybody leaves without a teardown.
+        store = dist.distributed_c10d._get_default_store()
+        if rank != 0:
+            import datetime
+            try:
+                store.wait(['dgmc_bench_done'], datetime.timedelta(seconds=900))
+            except Exception:
+                pass
+            sys.stderr.flush()
+            os._exit(0)
     out = None
     if rank == 0:
         peaks = load_peaks()
@@ -391,8 +433,10 @@ def main():
         out = {
             'metric': METRIC, 'value': value, 'unit': 'steps/s', 'n_gpus': world, 'steps': args.steps,
             'warmup': args.warmup, 'ms_per_step': ms_per_step, 'higher_is_better': True,
-            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-            'config': dict(config, parallelism='replicas x%d' % world if world > 1 else 'single GPU',
+            'scaling': 'strong' if world > 1 else 'weak', 'vs_baseline': None, 'dtype': 'f32',
+            'data': 'synthetic',
+            'config': dict(config, parallelism=('source rows sharded over %d GPUs, r_t all-reduce per consensus step '
+                                        '(NCCL), psi replicated' % world) if world > 1 else 'single GPU',
                            execution='whole step (zero_grad+fwd+loss+bwd+Adam) replayed as one CUDA '
                                      'graph (dgmc.utils.GraphedTrainStep); eager_ms_per_step is the '
                                      'same step issued from Python',
@@ -411,10 +455,12 @@ def main():
                 'value': sps, 'unit': 'steps/s', 'cores': cores, 'kind': 'port',
                 'sample': '%d full step(s) of the same workload after 1 warm-up, oracle port of the '
                           'reference (torch CPU, chunked matmul+topk), %.1f s/step' % (n, dt)}
-        print(json.dumps(out))
+        emit(out)
     if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+        store.set('dgmc_bench_done', '1')
+        sys.stderr.flush()
+        time.sleep(1.0)
+        os._exit(0)
     return 0
 
 

@@ -44,7 +44,11 @@ class GraphedTrainStep(object):
         torch.cuda.synchronize()
         if not structure_is_static:
             ops.clear_caches()  # so that the CSR builds are captured and re-run on new inputs
-        with torch.cuda.graph(self.graph):
+        # with NCCL collectives inside the step, the communicator's watchdog thread keeps polling
+        # CUDA events while this thread captures: only this thread's calls may be checked
+        import torch.distributed as dist
+        mode = 'thread_local' if dist.is_available() and dist.is_initialized() else 'global'
+        with torch.cuda.graph(self.graph, capture_error_mode=mode):
             self.loss = self._step()
         if not structure_is_static:
             ops.clear_caches()  # entries made during capture point into the graph's private pool
@@ -54,6 +58,8 @@ class GraphedTrainStep(object):
         S_0, S_L = self.model(*self.static)
         loss = self.loss_fn(S_0, S_L, self.static[-1])
         loss.backward()
+        if hasattr(self.model, 'sync_gradients'):  # RowShardedDGMC: sum partial gradients
+            self.model.sync_gradients()
         self.optimizer.step()
         return loss.detach()
 
