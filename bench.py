@@ -192,6 +192,7 @@ def timed(fn, iters, flush=None):
     """Average device time (ms) of fn over `iters` launches, CUDA events on the current stream;
     `flush` (a >L2 buffer) is rewritten before every launch so each one starts with a cold L2."""
     total = 0.0
+    fn()  # untimed: lazy one-time set-up (cached CSRs, kernel attributes) must not be measured
     for _ in range(iters):
         if flush is not None:
             flush.zero_()

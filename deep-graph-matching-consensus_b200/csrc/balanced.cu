@@ -5,12 +5,13 @@
 // SEGMENT then waits ~340 us on the longest one (ncu, profiles/README.md r1c).  Here the unit of
 // work is a block of DGMC_CSR_BLOCK = 32 consecutive ENTRIES: a group of G lanes first prefetches
 // the block's metadata (segment id, source row, weight of every entry: 32/G coalesced loads per
-// lane, nothing dependent on a previous gather), then streams the 32 source rows four at a time,
+// lane, nothing dependent on a previous gather), then streams the 32 source rows eight at a time,
 // switching accumulator whenever the segment id changes.  Control flow is the same for every group
-// of a warp (8 batches), so groups do not serialise each other.  A segment that lies inside one
+// of a warp (4 batches), so groups do not serialise each other.  A segment that lies inside one
 // block is written straight to the output; pieces of a segment that spans several blocks go to a
 // small partial buffer (at most two pieces per block: one that starts at the block start, one that
-// runs to the block end) and a second kernel adds them up in order — deterministic, no atomics.
+// runs to the block end) and a second kernel (one group per BLOCK) adds them up in order —
+// deterministic, no atomics.  Segments without entries are zeroed by the block after the gap.
 //
 //   MODE 0: out[s]  = seg_scale[s] * sum_e w_e * x[row_e]                (K4 transport, K5 aggregation)
 //   MODE 1: d_pt[t] = -w2 (.) sum_e g[perm[e]] * [ps[perm[e]/k] > pt[t]]  (K6 backward, target side)
@@ -35,6 +36,7 @@ struct BalArgs {
 template <int G, int NV, int MODE>
 __global__ void __launch_bounds__(256) balanced_main_kernel(const BalArgs a) {
     constexpr int PER = CB / G;  // metadata entries held per lane
+    constexpr int BR = NV <= 2 ? 8 : 4;  // source rows in flight per lane group
     const int lane = threadIdx.x & 31, gl = lane % G;
     const unsigned gmask = G == 32 ? 0xffffffffu : (((1u << G) - 1u) << (lane - gl));
     const long long groups = (long long)gridDim.x * (blockDim.x / G);
@@ -116,35 +118,48 @@ __global__ void __launch_bounds__(256) balanced_main_kernel(const BalArgs a) {
                 }
             }
         };
+        // empty segments produce no entries: the block holding the first entry AFTER a gap zeroes it
+        auto zero_rows = [&](long long s0, long long s1) {   // rows s0 .. s1-1
+            if (a.accumulate) return;
+            for (long long s = s0; s < s1; ++s)
+#pragma unroll
+                for (int v = 0; v < NV; ++v) {
+                    const int q = gl + v * G;
+                    if (q < a.r4)
+                        *reinterpret_cast<float4*>(a.out + (size_t)s * a.ldo + 4 * q) = make_float4(0, 0, 0, 0);
+                }
+        };
+        if (before != first_seg) zero_rows((long long)before + 1, first_seg);
         load_own(cur);
-        // ---- stream the rows, four at a time ----------------------------------------------------
+        // ---- stream the rows, BR at a time (all BR gathers of a lane are in flight together) ------
 #pragma unroll
-        for (int batch = 0; batch < CB / 4; ++batch) {
-            if (batch * 4 < count) {
-                int sg[4], rows[4]; float wt[4];
+        for (int batch = 0; batch < CB / BR; ++batch) {
+            if (batch * BR < count) {
+                int sg[BR], rows[BR]; float wt[BR];
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    const int j = batch * 4 + u;          // compile-time after unrolling
+                for (int u = 0; u < BR; ++u) {
+                    const int j = batch * BR + u;          // compile-time after unrolling
                     const int srcl = (lane - gl) + (j % G);
                     sg[u] = __shfl_sync(gmask, m_seg[j / G], srcl);
                     rows[u] = __shfl_sync(gmask, m_row[j / G], srcl);
                     wt[u] = __shfl_sync(gmask, m_w[j / G], srcl);
                 }
-                float4 t[NV][4];
+                float4 t[NV][BR];
 #pragma unroll
                 for (int v = 0; v < NV; ++v) {
                     const int q = gl + v * G;
                     const float* base = MODE == 0 ? a.x : a.ps;
                     const long long ld = MODE == 0 ? a.ldx : (long long)r;
 #pragma unroll
-                    for (int u = 0; u < 4; ++u)
+                    for (int u = 0; u < BR; ++u)
                         t[v][u] = q < a.r4 ? ldg4(base + (size_t)rows[u] * ld + 4 * q) : make_float4(0, 0, 0, 0);
                 }
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {
+                for (int u = 0; u < BR; ++u) {
                     if (sg[u] < 0) continue;              // beyond the last entry
                     if (sg[u] != cur) {
                         flush(cur, false);
+                        zero_rows((long long)cur + 1, sg[u]);
                         cur = sg[u];
                         at_block_start = false;
 #pragma unroll
@@ -167,36 +182,31 @@ __global__ void __launch_bounds__(256) balanced_main_kernel(const BalArgs a) {
             }
         }
         flush(cur, true);
+        if (e_begin + count >= a.nnz) zero_rows((long long)cur + 1, a.n_seg);  // trailing empty segments
     }
 }
 
-// one lane group per segment: empty segments -> zeros; segments spanning several entry blocks ->
-// ordered sum of their pieces
+// One lane group per entry block: if the block holds the FIRST piece of a segment that runs on into
+// later blocks, add that segment's pieces up in block order and write the result.
 template <int G, int NV>
 __global__ void __launch_bounds__(256) balanced_fixup_kernel(const BalArgs a, int apply_seg_scale) {
     const int gl = threadIdx.x % G;
     const long long groups = (long long)gridDim.x * (blockDim.x / G);
+    const long long nblk = (a.nnz + CB - 1) / CB;
     const int r = a.r4 * 4;
-    for (long long s = (long long)blockIdx.x * (blockDim.x / G) + threadIdx.x / G; s < a.n_seg; s += groups) {
-        const long long p0 = __ldg(a.ptr + s), p1 = __ldg(a.ptr + s + 1);
-        if (p0 == p1) {
-            if (!a.accumulate) {
-#pragma unroll
-                for (int v = 0; v < NV; ++v) {
-                    const int q = gl + v * G;
-                    if (q < a.r4)
-                        *reinterpret_cast<float4*>(a.out + (size_t)s * a.ldo + 4 * q) = make_float4(0, 0, 0, 0);
-                }
-            }
-            continue;
-        }
-        const long long b0 = p0 / CB, b1 = (p1 - 1) / CB;
-        if (b0 == b1) continue;  // written by the main kernel
+    for (long long b = (long long)blockIdx.x * (blockDim.x / G) + threadIdx.x / G; b < nblk; b += groups) {
+        const long long e_begin = b * CB;
+        const long long e_end = e_begin + CB < a.nnz ? e_begin + CB : a.nnz;
+        if (e_end >= a.nnz) continue;                           // last block: nothing runs on
+        const int s = __ldg(a.seg_of + e_end - 1);
+        if (__ldg(a.seg_of + e_end) != s) continue;             // last segment ends with the block
+        const bool whole = __ldg(a.seg_of + e_begin) == s;      // the piece starts at the block start
+        if (whole && e_begin > 0 && __ldg(a.seg_of + e_begin - 1) == s) continue;  // not the first piece
         float4 acc[NV];
 #pragma unroll
         for (int v = 0; v < NV; ++v) acc[v] = make_float4(0, 0, 0, 0);
-        for (long long b = b0; b <= b1; ++b) {
-            const long long slot = 2 * b + ((b == b0 && p0 != b0 * CB) ? 1 : 0);
+        long long slot = 2 * b + (whole ? 0 : 1);
+        for (long long bb = b;;) {
 #pragma unroll
             for (int v = 0; v < NV; ++v) {
                 const int q = gl + v * G;
@@ -205,6 +215,10 @@ __global__ void __launch_bounds__(256) balanced_fixup_kernel(const BalArgs a, in
                     acc[v].x += t.x; acc[v].y += t.y; acc[v].z += t.z; acc[v].w += t.w;
                 }
             }
+            ++bb;
+            const long long nb = bb * CB;                        // first entry of the next block
+            if (nb >= a.nnz || __ldg(a.seg_of + nb) != s) break;
+            slot = 2 * bb;
         }
         const float sc = (apply_seg_scale && a.seg_scale) ? __ldg(a.seg_scale + s) : 1.f;
 #pragma unroll
@@ -220,14 +234,26 @@ __global__ void __launch_bounds__(256) balanced_fixup_kernel(const BalArgs a, in
     }
 }
 
+// nnz == 0: every segment is empty
+__global__ void __launch_bounds__(256) balanced_zero_kernel(const BalArgs a) {
+    const long long total = a.n_seg * a.r4;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += stride)
+        *reinterpret_cast<float4*>(a.out + (size_t)(t / a.r4) * a.ldo + 4 * (t % a.r4)) = make_float4(0, 0, 0, 0);
+}
+
 template <int MODE>
 static int launch_balanced(const BalArgs& a, cudaStream_t stream) {
     const long long nblk = (a.nnz + CB - 1) / CB;
+    if (nblk == 0) {
+        if (!a.accumulate) balanced_zero_kernel<<<wave_grid(a.n_seg * a.r4, 256, 8), 256, 0, stream>>>(a);
+        return check_launch("balanced segmented reduction (empty)", a.accumulate ? 0 : 1);
+    }
 #define BAL(G, NV)                                                                                  \
     do {                                                                                            \
-        if (nblk > 0)                                                                               \
-            balanced_main_kernel<G, NV, MODE><<<wave_grid(nblk, 256 / G, 8), 256, 0, stream>>>(a); \
-        balanced_fixup_kernel<G, NV><<<wave_grid(a.n_seg, 256 / G, 8), 256, 0, stream>>>(a, MODE == 0); \
+        balanced_main_kernel<G, NV, MODE><<<wave_grid(nblk, 256 / G, 8), 256, 0, stream>>>(a);     \
+        if (nblk > 1)                                                                               \
+            balanced_fixup_kernel<G, NV><<<wave_grid(nblk, 256 / G, 8), 256, 0, stream>>>(a, MODE == 0); \
     } while (0)
     if (a.r4 <= 8) BAL(8, 1);
     else if (a.r4 <= 16) BAL(16, 1);
@@ -235,7 +261,7 @@ static int launch_balanced(const BalArgs& a, cudaStream_t stream) {
     else if (a.r4 <= 64) BAL(32, 2);
     else BAL(32, 4);
 #undef BAL
-    return check_launch("balanced segmented reduction", nblk > 0 ? 2 : 1);
+    return check_launch("balanced segmented reduction", nblk > 1 ? 2 : 1);
 }
 
 }  // namespace dgmc

@@ -34,28 +34,43 @@ __global__ void __launch_bounds__(WG_THREADS) wgrad_partial_kernel(
     float bsum = 0.f;  // thread `tid` < 64 owns column m0 + tid of db (only when blockIdx.x == 0)
     const bool g_vec = (ldg_ % 4 == 0) && ((reinterpret_cast<uintptr_t>(g) & 15) == 0) && (m0 + WG_TM <= M);
     const bool x_vec = (ldx % 4 == 0) && ((reinterpret_cast<uintptr_t>(x) & 15) == 0) && (n0 + WG_TN <= N);
-    for (long long k0 = k_begin; k0 < k_end; k0 += WG_KC) {
-        // stage [KC x 64] of G and of X (zero beyond the matrix / the slice)
-        for (int t = tid; t < WG_KC * 16; t += WG_THREADS) {
+    // software pipeline: the next [KC x 64] slabs of G and X travel global -> registers while the
+    // current ones are consumed from shared memory
+    constexpr int PF = WG_KC * 16 / WG_THREADS;  // float4 per thread and matrix
+    float4 pg[PF], px[PF];
+    auto fetch = [&](long long k0) {
+#pragma unroll
+        for (int p = 0; p < PF; ++p) {
+            const int t = tid + p * WG_THREADS;
             const int kk = t / 16, c = (t % 16) * 4;
             const long long k = k0 + kk;
             float4 vg = make_float4(0, 0, 0, 0), vx = make_float4(0, 0, 0, 0);
             if (k < k_end) {
                 if (g_vec) vg = ldg4(g + k * ldg_ + m0 + c);
                 else {
-                    float* p = &vg.x;
-                    for (int u = 0; u < 4; ++u) if (m0 + c + u < M) p[u] = __ldg(g + k * ldg_ + m0 + c + u);
+                    float* q = &vg.x;
+                    for (int u = 0; u < 4; ++u) if (m0 + c + u < M) q[u] = __ldg(g + k * ldg_ + m0 + c + u);
                 }
                 if (x_vec) vx = ldg4(x + k * ldx + n0 + c);
                 else {
-                    float* p = &vx.x;
-                    for (int u = 0; u < 4; ++u) if (n0 + c + u < N) p[u] = __ldg(x + k * ldx + n0 + c + u);
+                    float* q = &vx.x;
+                    for (int u = 0; u < 4; ++u) if (n0 + c + u < N) q[u] = __ldg(x + k * ldx + n0 + c + u);
                 }
             }
-            *reinterpret_cast<float4*>(&sg[kk][c]) = vg;
-            *reinterpret_cast<float4*>(&sx[kk][c]) = vx;
+            pg[p] = vg; px[p] = vx;
+        }
+    };
+    if (k_begin < k_end) fetch(k_begin);
+    for (long long k0 = k_begin; k0 < k_end; k0 += WG_KC) {
+#pragma unroll
+        for (int p = 0; p < PF; ++p) {
+            const int t = tid + p * WG_THREADS;
+            const int kk = t / 16, c = (t % 16) * 4;
+            *reinterpret_cast<float4*>(&sg[kk][c]) = pg[p];
+            *reinterpret_cast<float4*>(&sx[kk][c]) = px[p];
         }
         __syncthreads();
+        if (k0 + WG_KC < k_end) fetch(k0 + WG_KC);
 #pragma unroll 8
         for (int kk = 0; kk < WG_KC; ++kk) {
             const float4 a0 = *reinterpret_cast<const float4*>(&sg[kk][tm]);
@@ -110,7 +125,7 @@ __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* __restri
 
 static int wgrad_splits(long long K, int M, int N) {
     const int tiles = ((N + WG_TN - 1) / WG_TN) * ((M + WG_TM - 1) / WG_TM);
-    int splits = (2 * sm_count() + tiles - 1) / tiles;
+    int splits = (4 * sm_count() + tiles - 1) / tiles;   // ~4 CTAs of 128 threads per SM
     const long long max_by_k = (K + 4 * WG_KC - 1) / (4 * WG_KC);  // at least 128 rows per split
     if (splits > max_by_k) splits = (int)max_by_k;
     if (splits < 1) splits = 1;

@@ -25,11 +25,13 @@ class RelConv(torch.nn.Module):
         for lin in (self.lin1, self.lin2, self.root):
             lin.reset_parameters()
 
-    def forward(self, x, edge_index):
+    def forward(self, x, edge_index, relu=False):
+        """relu=True additionally applies the ReLU that RelCNN puts after every conv (rel.py:84-85),
+        fused into the GEMM epilogue."""
         graph = ops.GraphCSR.of(edge_index, x.size(0))
         stacked = ops.rel_aggregate(x, graph)  # [N, 3 C_in] = [x | mean_in | mean_out]
         weight = torch.cat([self.root.weight, self.lin1.weight, self.lin2.weight], dim=1)
-        return ops.node_linear(stacked, weight, self.root.bias)
+        return ops.node_linear(stacked, weight, self.root.bias, relu=relu)
 
     def __repr__(self):
         return '{}({}, {})'.format(type(self).__name__, self.in_channels, self.out_channels)
@@ -65,7 +67,7 @@ class RelCNN(torch.nn.Module):
     def forward(self, x, edge_index, *args):
         feats = [x]
         for conv, norm in zip(self.convs, self.batch_norms):
-            h = F.relu(conv(feats[-1], edge_index))
+            h = conv(feats[-1], edge_index, relu=True)
             if self.batch_norm:
                 h = norm(h)
             feats.append(F.dropout(h, p=self.dropout, training=self.training))

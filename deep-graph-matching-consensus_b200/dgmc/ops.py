@@ -79,6 +79,7 @@ class GraphCSR(object):
         src = edge_index[0].to(torch.int32).contiguous()
         dst = edge_index[1].to(torch.int32).contiguous()
         self.num_nodes, self.num_edges = num_nodes, src.numel()
+        self.src, self.dst = src, dst
         self.in_ptr, self.in_edge, self.in_seg = csr_build(dst, num_nodes, True)
         self.out_ptr, self.out_edge, self.out_seg = csr_build(src, num_nodes, True)
         self.in_nbr = src[self.in_edge.long()].contiguous()
@@ -86,6 +87,13 @@ class GraphCSR(object):
         deg_in = (self.in_ptr[1:] - self.in_ptr[:-1]).clamp_(min=1).to(torch.float32)
         deg_out = (self.out_ptr[1:] - self.out_ptr[:-1]).clamp_(min=1).to(torch.float32)
         self.inv_in, self.inv_out = deg_in.reciprocal_(), deg_out.reciprocal_()
+
+    @property
+    def rel(self):
+        """CSR of the [3N, N] RelConv aggregation matrix (see _RelAggregate) and of its transpose."""
+        if getattr(self, '_rel', None) is None:
+            self._rel = _RelOperator(self)
+        return self._rel
 
     @classmethod
     def of(cls, edge_index, num_nodes):
@@ -98,6 +106,20 @@ class GraphCSR(object):
             hit = (edge_index, cls(edge_index, num_nodes))
             cls._cache[key] = hit
         return hit[1]
+
+
+class _RelOperator(object):
+    def __init__(self, graph):
+        n, dev = graph.num_nodes, graph.in_ptr.device
+        src, dst = graph.src, graph.dst
+        node = torch.arange(n, dtype=torch.int32, device=dev)
+        rows = torch.cat([3 * node, 3 * dst + 1, 3 * src + 2])          # segment of A
+        cols = torch.cat([node, src, dst])
+        w = torch.cat([torch.ones(n, device=dev), graph.inv_in[dst.long()], graph.inv_out[src.long()]])
+        self.f_ptr, perm, self.f_seg = csr_build(rows, 3 * n, True)
+        self.f_src, self.f_w = cols[perm.long()].contiguous(), w[perm.long()].contiguous()
+        self.b_ptr, perm, self.b_seg = csr_build(cols, n, True)
+        self.b_src, self.b_w = rows[perm.long()].contiguous(), w[perm.long()].contiguous()
 
 
 class MergedPair(object):
@@ -327,14 +349,23 @@ def diff_mlp(s_hat, ps, pt, w2, b2, cand):
 # --------------------------------------------------------------------------------------------
 class _NodeLinear(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias):
-        ctx.save_for_backward(x, weight)
-        ctx.has_bias = bias is not None
-        return torch.addmm(bias, x, weight.t()) if bias is not None else x @ weight.t()
+    def forward(ctx, x, weight, bias, relu):
+        if relu:  # bias + ReLU in the library GEMM's epilogue
+            y = torch._addmm_activation(bias, x, weight.t(), use_gelu=False)
+            ctx.save_for_backward(x, weight, y)
+        else:
+            y = torch.addmm(bias, x, weight.t()) if bias is not None else x @ weight.t()
+            ctx.save_for_backward(x, weight)
+        ctx.has_bias, ctx.relu = bias is not None, relu
+        return y
 
     @staticmethod
     def backward(ctx, g):
-        x, weight = ctx.saved_tensors
+        if ctx.relu:
+            x, weight, y = ctx.saved_tensors
+            g = g * (y > 0)
+        else:
+            x, weight = ctx.saved_tensors
         g = _f32(g)
         k, m, n = x.size(0), weight.size(0), weight.size(1)
         dx = g @ weight if ctx.needs_input_grad[0] else None
@@ -345,48 +376,46 @@ class _NodeLinear(torch.autograd.Function):
             ws = _workspace(query('dgmc_wgrad_workspace', k, m, n), g.device)
             call('dgmc_wgrad', g, g.stride(0), RowStrided(x), x.stride(0), k, m, n, dw, db, ws,
                  ws.numel(), stream_ptr())
-        return dx, dw, db
+        return dx, dw, db, None
 
 
-def node_linear(x, weight, bias=None):
-    """x [nodes, in] @ weight[out, in]^T (+ bias): library GEMM forward and input gradient; the
-    weight / bias gradient (a reduction over all nodes with a tiny output) runs on the split-K kernel
-    dgmc_wgrad when the output is small, else stays with the library."""
+def node_linear(x, weight, bias=None, relu=False):
+    """relu?(x [nodes, in] @ weight[out, in]^T + bias): library GEMM forward (bias and ReLU in its
+    epilogue) and input gradient; the weight / bias gradient (a reduction over all nodes with a tiny
+    output) runs on the split-K kernel dgmc_wgrad when the output is small, else stays with the
+    library."""
     if weight.size(0) * weight.size(1) <= 64 * 1024 and x.size(0) >= 2048 and x.is_cuda \
-            and x.dtype == torch.float32 and x.stride(1) == 1:
-        return _NodeLinear.apply(x, weight, bias)
-    return torch.nn.functional.linear(x, weight, bias)
+            and x.dtype == torch.float32 and x.stride(1) == 1 and (bias is not None or not relu):
+        return _NodeLinear.apply(x, weight, bias, relu)
+    y = torch.nn.functional.linear(x, weight, bias)
+    return torch.relu(y) if relu else y
 
 
 # --------------------------------------------------------------------------------------------
 # K5: RelConv mean aggregation in both flow directions
 # --------------------------------------------------------------------------------------------
 class _RelAggregate(torch.autograd.Function):
+    """[x | mean_in x | mean_out x] as ONE sparse product A x with A of shape [3N, N]: row 3i is
+    e_i, row 3i+1 the in-neighbour mean of node i, row 3i+2 its out-neighbour mean — the row-major
+    [3N, C] result IS the [N, 3C] operand of the layer GEMM.  Backward is A^T g with g viewed as
+    [3N, C].  Both directions therefore cost one balanced segmented gather (+ its fix-up)."""
     @staticmethod
     def forward(ctx, x, graph):
         x = _f32(x)
         n, c = x.shape
+        rel = graph.rel
         cat = torch.empty(n, 3 * c, dtype=torch.float32, device=x.device)
-        cat[:, :c] = x
-        segment_gather(x, n, graph.in_nbr, ptr=graph.in_ptr, seg_scale=graph.inv_in,
-                       out=cat[:, c:2 * c], seg_of=graph.in_seg)
-        segment_gather(x, n, graph.out_nbr, ptr=graph.out_ptr, seg_scale=graph.inv_out,
-                       out=cat[:, 2 * c:], seg_of=graph.out_seg)
-        ctx.graph, ctx.c = graph, c
+        segment_gather(x, 3 * n, rel.f_src, ptr=rel.f_ptr, w=rel.f_w, out=cat.view(3 * n, c),
+                       seg_of=rel.f_seg)
+        ctx.graph = graph
         return cat
 
     @staticmethod
     def backward(ctx, g):
-        graph, c = ctx.graph, ctx.c
+        rel = ctx.graph.rel
         g = _f32(g)
-        n = g.size(0)
-        dx = g[:, :c].contiguous()
-        # transpose of mean-in: dx[j] += sum_{e: j -> i} inv_in[i] g_in[i]
-        segment_gather(g[:, c:2 * c], n, graph.out_nbr, ptr=graph.out_ptr, src_scale=graph.inv_in,
-                       out=dx, accumulate=True, seg_of=graph.out_seg)
-        # transpose of mean-out: dx[j] += sum_{e: i -> j} inv_out[i] g_out[i]
-        segment_gather(g[:, 2 * c:], n, graph.in_nbr, ptr=graph.in_ptr, src_scale=graph.inv_out,
-                       out=dx, accumulate=True, seg_of=graph.in_seg)
+        n, c = g.size(0), g.size(1) // 3
+        dx = segment_gather(g.view(3 * n, c), n, rel.b_src, ptr=rel.b_ptr, w=rel.b_w, seg_of=rel.b_seg)
         return dx, None
 
 
