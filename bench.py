@@ -205,56 +205,79 @@ def timed(fn, iters, flush=None):
     return total / iters
 
 
-def kernel_rooflines(w, model, d, peaks, step_ms):
-    """Times each hot kernel alone (cold L2) on step-shaped data; algorithmic bytes / flops per
-    launch follow SURVEY.md §8(d) (tables here are smaller than L2, so bytes_alg = bytes_min)."""
+def kernel_rooflines(w, model, e_t, peaks, step_ms, iters=5):
+    """Times each hot kernel alone (cold L2) on step-shaped data.  Algorithmic bytes / flops per
+    launch follow SURVEY.md §8(d): `bytes_min` (every operand read once, every result written once)
+    when the gathered table fits in L2, else `bytes_logical` (gathered rows counted per access)."""
     from dgmc import ops
-    dev = d['x_s'].device
+    dev = e_t.device
     n_s, n_t, C, R, k = w['n_s'], w['n_t'], w['dim'], w['rnd_dim'], w['k']
     k_eff = k + min(k, n_t - k)
     L, T = w['layers'], w['num_steps']
+    l2 = torch.cuda.get_device_properties(dev).L2_cache_size
     g = torch.Generator(device='cpu').manual_seed(3)
-    h_s = torch.randn(1, n_s, C, generator=g).to(dev)
-    h_t = torch.randn(1, n_t, C, generator=g).to(dev)
+
+    def rnd(*shape):
+        return torch.randn(*shape, generator=g, dtype=torch.float32).to(dev)
+
+    h_s, h_t = rnd(1, n_s, C), rnd(1, n_t, C)
     idx = torch.randint(n_t, (1, n_s, k_eff), generator=g).to(dev)
     cand = ops.Candidates(idx, n_t)
     cand.csr
     S = torch.rand(n_s, k_eff, generator=g).to(dev)
-    r_s = torch.randn(n_s, R, generator=g).to(dev)
-    p_s, p_t = torch.randn(n_s, R, generator=g).to(dev), torch.randn(n_t, R, generator=g).to(dev)
-    w2, b2 = torch.randn(R, generator=g).to(dev), torch.zeros(1, device=dev)
-    graph_t = ops.GraphCSR.of(d['e_t'], n_t)
-    x_t = torch.randn(n_t, R, generator=g).to(dev)
+    r_s, p_s, p_t, x_t = rnd(n_s, R), rnd(n_s, R), rnd(n_t, R), rnd(n_t, R)
+    w2, b2 = rnd(R), torch.zeros(1, device=dev)
+    graph_t = ops.GraphCSR.of(e_t, n_t)
+    E = e_t.size(1)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
-    model_k = model.k
     hbm, tf = peaks['hbm_gbs'], peaks['bf16_tflops']
     rows = []
 
-    def add(name, fn, calls, unit_work, bound):
-        ms = timed(fn, 5, flush)
-        achieved = unit_work / (ms * 1e-3) / (1e12 if bound == 'tensor' else 1e9)
+    def pick(table_bytes, b_min, b_logical):
+        return (b_logical, 'logical') if table_bytes > l2 else (b_min, 'min')
+
+    def add(name, fn, calls, work, bound, basis=''):
+        ms = timed(fn, iters, flush)
+        achieved = work / (ms * 1e-3) / (1e12 if bound == 'tensor' else 1e9)
         peak = tf if bound == 'tensor' else hbm
         rows.append({'kernel': name, 'bound': bound, 'achieved': round(achieved, 2), 'peak': peak,
                      'unit': 'TFLOP/s' if bound == 'tensor' else 'GB/s',
-                     'frac': round(achieved / peak, 4), 'traffic': None,
+                     'frac': round(achieved / peak, 4), 'traffic': None, 'work_basis': basis,
                      'ms_per_launch': round(ms, 4), 'launches_per_step': calls,
-                     'share_of_step': round(ms * calls / step_ms, 4)})
+                     'share_of_step': round(ms * calls / step_ms, 4) if step_ms else None})
 
     with torch.no_grad():
-        add('K1 top-k (dgmc_topk_*)', lambda: model.__top_k__(h_s, h_t), 1,
-            2.0 * n_s * n_t * C, 'tensor')
-        add('K2 gather_dot', lambda: ops.gather_dot(h_s[0], h_t[0], cand), 1,
-            (n_s + n_t) * 4 * C + 8 * n_s * k_eff, 'hbm')
-        add('K3 softmax_k fwd', lambda: ops.softmax_k(S), T + 2, 8 * n_s * k_eff, 'hbm')
-        add('K4 transport (segment_gather by target)', lambda: ops.transport(S, r_s, cand), T,
-            8 * n_s * k_eff + 4 * R * (n_s + n_t), 'hbm')
-        add('K5 rel_aggregate (2 segment_gathers, target graph)',
-            lambda: ops.rel_aggregate(x_t, graph_t), 2 * L * T,
-            8 * n_t * R + 8 * w['e_t'] + 8 * n_t, 'hbm')
-        add('K6 diff_mlp fwd', lambda: ops.diff_mlp(S, p_s, p_t, w2, b2, cand), T,
-            4 * R * (n_s + n_t) + 12 * n_s * k_eff, 'hbm')
-    model.k = model_k
+        add('K1 top-k (cast + tcgen05 GEMM/select + fp32 merge)', lambda: model.__top_k__(h_s, h_t), 1,
+            2.0 * n_s * n_t * C, 'tensor', '2*N_s*N_t*C flop')
+        wk, b = pick(n_t * 4 * C, (n_s + n_t) * 4 * C + 8 * n_s * k_eff,
+                     4 * C * n_s * (1 + k_eff) + 8 * n_s * k_eff)
+        add('K2 gather_dot', lambda: ops.gather_dot(h_s[0], h_t[0], cand), 1, wk, 'hbm', b)
+        add('K3 softmax_k fwd', lambda: ops.softmax_k(S), T + 2, 8 * n_s * k_eff, 'hbm', 'min')
+        wk, b = pick(n_s * 4 * R, 8 * n_s * k_eff + 4 * R * (n_s + n_t),
+                     8 * n_s * k_eff + 4 * R * n_s * (1 + 2 * k_eff))
+        add('K4 transport (balanced segmented gather by target)', lambda: ops.transport(S, r_s, cand), T,
+            wk, 'hbm', b)
+        wk, b = pick(n_t * 4 * R, 8 * n_t * R + 8 * E + 8 * n_t, 8 * n_t * R + 2 * E * (4 * R + 4))
+        add('K5 rel_aggregate ([3N,N] sparse product, target graph)',
+            lambda: ops.rel_aggregate(x_t, graph_t), L * T, wk, 'hbm', b)
+        wk, b = pick(n_t * 4 * R, 4 * R * (n_s + n_t) + 12 * n_s * k_eff,
+                     4 * R * n_s * (1 + k_eff) + 12 * n_s * k_eff)
+        add('K6 diff_mlp fwd', lambda: ops.diff_mlp(S, p_s, p_t, w2, b2, cand), T, wk, 'hbm', b)
     return rows
+
+
+def scale_kernels(n, dev):
+    """`--scale-kernels N`: the hot kernels alone on an N x N-node synthetic pair (BASELINE.json
+    configs[4] shape at N = 1,000,000: 256-d embeddings, R = 64, k_eff = 20, 5 out-edges per node),
+    where the gathered tables no longer fit in L2 and HBM is the roofline."""
+    from dgmc.models import DGMC, RelCNN
+    w = dict(n_s=n, n_t=n, dim=256, rnd_dim=64, k=10, layers=3, num_steps=10)
+    g = torch.Generator().manual_seed(11)
+    e_t = torch.randint(n, (2, 5 * n), generator=g).to(dev)
+    model = DGMC(RelCNN(8, 8, 1), RelCNN(64, 64, 1), num_steps=10, k=10).to(dev)
+    rows = kernel_rooflines(w, model, e_t, load_peaks(), None, iters=3)
+    emit({'scale_kernels': {'n_s': n, 'n_t': n, 'C': 256, 'R': 64, 'k_eff': 20, 'edges': 5 * n},
+          'roofline_all': rows})
 
 
 def stage(msg):
@@ -280,6 +303,8 @@ def main():
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--cpu-budget', type=float, default=None, help='seconds of CPU baseline work')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--scale-kernels', type=int, default=0, metavar='N',
+                    help='time the hot kernels alone on an N x N-node pair and exit')
     ap.add_argument('--profile-eager', action='store_true',
                     help='warm up, run --steps eager steps inside the NVTX range "timed_step" and exit '
                          '(for ncu --nvtx --nvtx-include "timed_step/")')
@@ -319,6 +344,9 @@ def main():
     import torch.distributed as dist
     torch.cuda.set_device(local)
     dev = torch.device('cuda', local)
+    if args.scale_kernels:
+        scale_kernels(args.scale_kernels, dev)
+        return 0
     if world > 1:
         os.environ.setdefault('TORCH_NCCL_ASYNC_ERROR_HANDLING', '0')  # collectives get graph-captured
         dist.init_process_group('nccl', device_id=dev)
@@ -427,7 +455,7 @@ def main():
     out = None
     if rank == 0:
         peaks = load_peaks()
-        rl = kernel_rooflines(w, model, d, peaks, ms_per_step)
+        rl = kernel_rooflines(w, model, d['e_t'], peaks, ms_per_step)
         top = max(rl, key=lambda r: r['share_of_step'])
         roofline = {k_: top[k_] for k_ in ('bound', 'achieved', 'peak', 'unit', 'frac', 'traffic')}
         roofline.update(kernel=top['kernel'], peak_source=peaks['source'] + ' (burst: kernel timed alone)')

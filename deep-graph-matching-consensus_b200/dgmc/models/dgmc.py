@@ -203,7 +203,7 @@ class DGMC(torch.nn.Module):
         outs = []
         for val in (S_0, S_L):
             sp = torch.sparse_coo_tensor(coords, val.reshape(-1), size,
-                                         requires_grad=val.requires_grad)
+                                         requires_grad=val.requires_grad, check_invariants=False)
             sp.__idx__, sp.__val__ = S_idx, val
             outs.append(sp)
         return outs[0], outs[1]

@@ -1,0 +1,166 @@
+"""Parity at sizes beyond the committed fixtures, against the CPU oracle run in the same test
+(seeded inputs, injected random draws), plus size-independent properties at the full DBP15K shape.
+
+ * DBP15K-lite (4,000 x 4,200 nodes, sparse k=10, training mode with negatives + ground truth,
+   3 consensus steps): goes through the tensor-core top-k kernel; S_0 / S_L / loss against the fp64
+   oracle with the fp32 oracle's own error as yardstick.
+ * PascalVOC-shaped ragged batch (64 graphs of 10-20 nodes, SplineCNN, dense, 2 steps).
+ * full DBP15K shape (19,388 x 19,572): rows of S sum to 1, candidates are the exact top-k on
+   sampled rows, S_0 is the softmax of the exact scores.
+"""
+import pytest
+import torch
+
+from helpers import assert_parity, replay_draws, sort_rows_by_index
+from oracle import dgmc_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def _rel_spec(c_in, c_out, layers):
+    s = dict(kind='rel', out=c_out, layers=layers, batch_norm=False, cat=True, lin=True, dropout=0.0)
+    s['in'] = c_in
+    return s
+
+
+def _load(model, params):
+    missing, unexpected = model.load_state_dict(params, strict=False)
+    assert not unexpected and all('batch_norm' in m for m in missing), (missing, unexpected)
+    return model
+
+
+def test_dbp15k_lite_sparse_training_step_against_oracle():
+    from dgmc.models import DGMC, RelCNN
+    g = torch.Generator().manual_seed(42)
+    n_s, n_t, feat, k, steps, R = 4000, 4200, 48, 10, 3, 16
+    x_s = torch.randn(n_s, feat, generator=g)
+    perm = torch.randperm(n_t, generator=g)[:n_s]
+    x_t = torch.randn(n_t, feat, generator=g)
+    x_t[perm] = x_s + 0.4 * torch.randn(n_s, feat, generator=g)
+    e_s = torch.randint(n_s, (2, 4 * n_s), generator=g)
+    e_t = torch.randint(n_t, (2, 4 * n_t), generator=g)
+    rows = torch.sort(torch.randperm(n_s, generator=g)[:900])[0]
+    y = torch.stack([rows, perm[rows]])
+    draws = {'neg': torch.randint(n_t, (1, n_s, k), generator=g),
+             'r_s': [torch.randn(1, n_s, R, generator=g) for _ in range(steps)]}
+    s1, s2 = _rel_spec(feat, 64, 2), _rel_spec(R, R, 2)
+    params = O.init_dgmc(7, s1, s2)
+
+    model = _load(DGMC(RelCNN(feat, 64, 2), RelCNN(R, R, 2), num_steps=steps, k=k), params).cuda().train()
+    dev = [t.cuda() for t in (x_s, e_s, x_t, e_t, y)]
+    with replay_draws(draws, 'cuda'):
+        S_0, S_L = model(dev[0], dev[1], None, None, dev[2], dev[3], None, None, dev[4])
+    loss = model.loss(S_L, dev[4])
+
+    def oracle(dtype, S_idx=None):
+        p = {n: v.to(dtype) for n, v in params.items()}
+        out = O.dgmc_forward(s1, s2, p, x_s.to(dtype), e_s, None, None, x_t.to(dtype), e_t, None, None,
+                             steps, k, y=y, training=True, draws=draws, topk_dtype=torch.float64,
+                             S_idx=S_idx)
+        out['loss'] = O.loss(out['S_L'], y, idx=out['idx'])
+        return out
+
+    ref64 = oracle(torch.float64)
+    gi, g0, gL = sort_rows_by_index(S_L.__idx__.cpu(), S_0.__val__.detach().cpu(), S_L.__val__.detach().cpu())
+    ri, r0, rL = sort_rows_by_index(ref64['idx'], ref64['S_0'], ref64['S_L'])
+    same = (gi == ri).all(dim=1)
+    # candidate sets: bit-exact except where the k-th / (k+1)-th gap is below 1e-6 relative
+    assert int((~same).sum()) <= 2, '%d rows differ' % int((~same).sum())
+    ref32 = oracle(torch.float32, S_idx=ref64['idx'].unsqueeze(0))
+    _, q0, qL = sort_rows_by_index(ref32['idx'], ref32['S_0'], ref32['S_L'])
+    assert_parity(g0[same], r0[same], q0[same], what='S_0')
+    assert_parity(gL[same], rL[same], qL[same], what='S_L')
+    if bool(same.all()):
+        assert_parity(loss, ref64['loss'], ref32['loss'], what='loss')
+
+
+def test_pascal_shaped_ragged_dense_batch_against_oracle():
+    from dgmc.models import DGMC, SplineCNN
+    g = torch.Generator().manual_seed(5)
+    B, feat, R, steps = 64, 32, 16, 2
+    sizes_s = torch.randint(10, 21, (B, ), generator=g).tolist()
+    sizes_t = [min(20, n + int(torch.randint(0, 3, (1, ), generator=g))) for n in sizes_s]
+
+    def batch(sizes):
+        xs, es, ats, bs, off = [], [], [], [], 0
+        for i, n in enumerate(sizes):
+            xs.append(torch.randn(n, feat, generator=g))
+            es.append(torch.randint(n, (2, 5 * n), generator=g) + off)
+            ats.append(torch.rand(5 * n, 2, generator=g))
+            bs.append(torch.full((n, ), i, dtype=torch.long))
+            off += n
+        return torch.cat(xs), torch.cat(es, 1), torch.cat(ats), torch.cat(bs)
+
+    x_s, e_s, a_s, b_s = batch(sizes_s)
+    x_t, e_t, a_t, b_t = batch(sizes_t)
+    n_max = max(sizes_s)
+    y = torch.stack([torch.arange(x_s.size(0)),
+                     torch.cat([torch.arange(n) % m for n, m in zip(sizes_s, sizes_t)])])
+    draws = {'neg': None, 'r_s': [torch.randn(B, n_max, R, generator=g) for _ in range(steps)]}
+    s1 = dict(kind='spline', out=48, dim=2, layers=2, cat=False, lin=True, dropout=0.0)
+    s1['in'] = feat
+    s2 = dict(kind='spline', out=R, dim=2, layers=2, cat=True, lin=True, dropout=0.0)
+    s2['in'] = R
+    params = O.init_dgmc(3, s1, s2)
+    model = _load(DGMC(SplineCNN(feat, 48, 2, 2, cat=False), SplineCNN(R, R, 2, 2, cat=True),
+                       num_steps=steps), params).cuda().train()
+    dev = [t.cuda() for t in (x_s, e_s, a_s, b_s, x_t, e_t, a_t, b_t)]
+    with replay_draws(draws, 'cuda'):
+        S_0, S_L = model(*dev)
+    loss = model.loss(S_0, y.cuda()) + model.loss(S_L, y.cuda())
+    loss.backward()
+
+    def oracle(dtype):
+        p = {n: v.to(dtype).requires_grad_() for n, v in params.items()}
+        out = O.dgmc_forward(s1, s2, p, x_s.to(dtype), e_s, a_s.to(dtype), b_s, x_t.to(dtype), e_t,
+                             a_t.to(dtype), b_t, steps, -1, training=True, draws=draws)
+        out['loss'] = O.loss(out['S_0'], y) + O.loss(out['S_L'], y)
+        out['loss'].backward()
+        out['grads'] = {n: v.grad for n, v in p.items()}
+        return out
+
+    r64, r32 = oracle(torch.float64), oracle(torch.float32)
+    assert_parity(S_0, r64['S_0'], r32['S_0'], what='S_0')
+    assert_parity(S_L, r64['S_L'], r32['S_L'], what='S_L')
+    assert_parity(loss, r64['loss'], r32['loss'], what='loss')
+    got = dict(model.named_parameters())
+    for n, gref in r64['grads'].items():
+        if gref is None:
+            continue
+        scale = gref.abs().max().item()
+        noise = (r32['grads'][n].double() - gref).abs().max().item()
+        err = (got[n].grad.double().cpu() - gref).abs().max().item()
+        assert err <= max(5e-4 * scale, 5 * noise) + 1e-9, (n, err, scale, noise)
+
+
+def test_full_dbp15k_shape_properties():
+    from dgmc.models import DGMC, RelCNN
+    g = torch.Generator().manual_seed(0)
+    n_s, n_t, feat, k = 19388, 19572, 300, 10
+    x_s = torch.randn(n_s, feat, generator=g)
+    perm = torch.randperm(n_t, generator=g)[:n_s]
+    x_t = torch.randn(n_t, feat, generator=g)
+    x_t[perm] = x_s + 0.5 * torch.randn(n_s, feat, generator=g)
+    e_s = torch.randint(n_s, (2, 70414), generator=g).cuda()
+    e_t = torch.randint(n_t, (2, 95142), generator=g).cuda()
+    torch.manual_seed(0)
+    model = DGMC(RelCNN(feat, 256, 3, dropout=0.5), RelCNN(64, 64, 3), num_steps=10, k=k).cuda().eval()
+    with torch.no_grad():
+        S_0, S_L = model(x_s.cuda(), e_s, None, None, x_t.cuda(), e_t, None, None)
+        h_s = model.psi_1(x_s.cuda(), e_s, None)
+        h_t = model.psi_1(x_t.cuda(), e_t, None)
+    ones = torch.ones(n_s, device='cuda')
+    assert torch.allclose(S_0.__val__.sum(-1), ones, atol=1e-5)
+    assert torch.allclose(S_L.__val__.sum(-1), ones, atol=1e-5)
+    assert S_L.__idx__.shape == (n_s, k) and int(S_L.__idx__.max()) < n_t and int(S_L.__idx__.min()) >= 0
+    assert bool((S_L.__idx__.sort(-1)[0][:, 1:] != S_L.__idx__.sort(-1)[0][:, :-1]).all())  # distinct
+    rows = torch.arange(0, n_s, 37, device='cuda')
+    exact = h_s[rows].double() @ h_t.double().t()
+    top_v, top_i = exact.topk(k + 1, dim=1)
+    safe = (top_v[:, k - 1] - top_v[:, k]) > 1e-6 * top_v[:, k - 1].abs()
+    same = (S_0.__idx__[rows].sort(-1)[0] == top_i[:, :k].sort(-1)[0]).all(-1)
+    assert bool(same[safe].all())
+    # S_0 = softmax of the exact candidate scores (dgmc.py:197-202)
+    picked = torch.gather(exact, 1, S_0.__idx__[rows])
+    assert torch.allclose(S_0.__val__[rows].double(), picked.softmax(-1), rtol=1e-4, atol=1e-6)
+    assert model.acc(S_L, torch.stack([torch.arange(n_s), perm]).cuda()) >= 0.0
