@@ -57,6 +57,16 @@ def _repad(x, mask):
     return out
 
 
+def _sparse_coo(coords, values, size):
+    """Un-coalesced COO tensor as the reference builds it (dgmc.py:234-240), without torch's
+    one-off 'invariant checks are implicitly disabled' warning."""
+    import warnings
+    with warnings.catch_warnings():
+        warnings.simplefilter('ignore', UserWarning)
+        return torch.sparse_coo_tensor(coords, values, size, requires_grad=values.requires_grad,
+                                       check_invariants=False)
+
+
 class DGMC(torch.nn.Module):
     r"""Deep Graph Matching Consensus: local matching with :obj:`psi_1`, then :obj:`num_steps`
     neighbourhood-consensus refinements with :obj:`psi_2`.  Same arguments, attributes, outputs
@@ -202,8 +212,7 @@ class DGMC(torch.nn.Module):
         size = torch.Size([n_rows, N_t])
         outs = []
         for val in (S_0, S_L):
-            sp = torch.sparse_coo_tensor(coords, val.reshape(-1), size,
-                                         requires_grad=val.requires_grad, check_invariants=False)
+            sp = _sparse_coo(coords, val.reshape(-1), size)
             sp.__idx__, sp.__val__ = S_idx, val
             outs.append(sp)
         return outs[0], outs[1]

@@ -9,10 +9,15 @@ S, and the K1/K2/K3/K4/K6 kernels that touch them — exist only for the rank's 
   * the indicator transport r_t = S^T r_s is a sum over source rows: each rank reduces its rows into
     a partial [N_t, R] and ONE all-reduce (NCCL over NVLink) per consensus step completes it; its
     backward is the matching all-reduce of d r_t;
-  * psi_1 / psi_2 run replicated on identical inputs (r_s is drawn at full shape from the shared
-    seed on every rank, as the reference's RNG contract requires), so their outputs agree bit for bit
-    and need no exchange; weight gradients are partial (each rank back-propagates its own rows'
-    loss) and are summed once per step by `sync_gradients()`.
+  * psi_2 (when it is this package's RelCNN without batch-norm statistics or dropout) is sharded by
+    NODES: each rank owns a block of source nodes (the same block as its rows of S) and a block of
+    target nodes, computes every RelConv layer only for those, and all-gathers the layer output
+    (its neighbours live on other ranks); the hoisted MLP projection of the target side, P_t, is
+    all-gathered once per step because the difference kernel gathers arbitrary target rows — the
+    "all-gather of o_t" of the north star.  Backward of an all-gather is a reduce-scatter.
+    Any other psi_2, and psi_1, run replicated on identical inputs (r_s is drawn at full shape from
+    the shared seed on every rank, as the reference's RNG contract requires);
+  * weight gradients are partial on every rank and are summed once per step by `sync_gradients()`.
 
 Results equal the single-GPU path up to the fp32 summation order of the all-reduce.
 """
@@ -20,7 +25,7 @@ import torch
 import torch.distributed as dist
 
 from .. import ops
-from .dgmc import DGMC, EPS, _rows
+from .dgmc import DGMC, EPS, _sparse_coo
 
 
 def row_block(n_rows, rank, world):
@@ -51,16 +56,124 @@ def all_reduce_sum(x, group=None):
     return _AllReduceSum.apply(x, group)
 
 
+class _AllGatherRows(torch.autograd.Function):
+    """[n, c] on every rank -> [world * n, c]; adjoint: reduce-scatter of the gradient."""
+    @staticmethod
+    def forward(ctx, x, group):
+        ctx.group = group
+        x = x.contiguous()
+        out = x.new_empty(dist.get_world_size(group) * x.size(0), x.size(1))
+        dist.all_gather_into_tensor(out, x, group=group)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        world = dist.get_world_size(ctx.group)
+        g = g.contiguous()
+        out = g.new_empty(g.size(0) // world, g.size(1))
+        dist.reduce_scatter_tensor(out, g, op=dist.ReduceOp.SUM, group=ctx.group)
+        return out, None
+
+
+def all_gather_rows(x, group=None):
+    return _AllGatherRows.apply(x, group)
+
+
+class ShardedPair(object):
+    """Node partition of the merged (source + target) graph over the ranks, and this rank's slice
+    of the RelConv aggregation operator.
+
+    Gathered layout: rank q contributes a block of `n_max` rows = [its source nodes | its target
+    nodes | padding]; `pos[v]` is the row of merged node v in that layout.  `rel` is the
+    [3 n_loc, world * n_max] operator (see ops._RelAggregate) restricted to this rank's nodes with
+    columns in the gathered layout.  Built once per (edge_index_s, edge_index_t) and cached."""
+    _cache = {}
+
+    def __init__(self, e_s, e_t, n_s, n_t, rank, world):
+        dev = e_s.device
+        blocks_s = [row_block(n_s, q, world) for q in range(world)]
+        blocks_t = [row_block(n_t, q, world) for q in range(world)]
+        self.n_max = max((b[1] - b[0]) + (c[1] - c[0]) for b, c in zip(blocks_s, blocks_t))
+        self.nt_max = max(c[1] - c[0] for c in blocks_t)
+        n = n_s + n_t
+        pos = torch.empty(n, dtype=torch.long, device=dev)
+        pos_t = torch.empty(n_t, dtype=torch.long, device=dev)   # target -> row of the gathered P_t
+        for q, (b, c) in enumerate(zip(blocks_s, blocks_t)):
+            pos[b[0]:b[1]] = q * self.n_max + torch.arange(b[1] - b[0], device=dev)
+            pos[n_s + c[0]:n_s + c[1]] = q * self.n_max + (b[1] - b[0]) + torch.arange(c[1] - c[0], device=dev)
+            pos_t[c[0]:c[1]] = q * self.nt_max + torch.arange(c[1] - c[0], device=dev)
+        self.pos_t = pos_t
+        src_of = torch.zeros(world * self.n_max, dtype=torch.long, device=dev)  # gathered row -> merged node
+        src_of[pos] = torch.arange(n, device=dev)
+        self.src_of = src_of
+        (lo_s, hi_s), (lo_t, hi_t) = blocks_s[rank], blocks_t[rank]
+        self.ns_loc, self.nt_loc = hi_s - lo_s, hi_t - lo_t
+        self.n_loc = self.ns_loc + self.nt_loc
+        local = torch.cat([torch.arange(lo_s, hi_s, device=dev), n_s + torch.arange(lo_t, hi_t, device=dev)])
+        self.local = local
+        loc_of = torch.full((n, ), -1, dtype=torch.long, device=dev)
+        loc_of[local] = torch.arange(self.n_loc, device=dev)
+        src = torch.cat([e_s[0], e_t[0] + n_s])
+        dst = torch.cat([e_s[1], e_t[1] + n_s])
+        inv_in = torch.bincount(dst, minlength=n).clamp_(min=1).to(torch.float32).reciprocal_()
+        inv_out = torch.bincount(src, minlength=n).clamp_(min=1).to(torch.float32).reciprocal_()
+        m_in, m_out = loc_of[dst] >= 0, loc_of[src] >= 0
+        rows = torch.cat([3 * torch.arange(self.n_loc, device=dev), 3 * loc_of[dst[m_in]] + 1,
+                          3 * loc_of[src[m_out]] + 2]).to(torch.int32)
+        cols = torch.cat([pos[local], pos[src[m_in]], pos[dst[m_out]]]).to(torch.int32)
+        w = torch.cat([torch.ones(self.n_loc, device=dev), inv_in[dst[m_in]], inv_out[src[m_out]]])
+        rel = type('RelSlice', (), {})()
+        rel.n_out, rel.n_in = self.n_loc, world * self.n_max
+        rel.f_ptr, perm, rel.f_seg = ops.csr_build(rows, 3 * rel.n_out, True)
+        rel.f_src, rel.f_w = cols[perm.long()].contiguous(), w[perm.long()].contiguous()
+        rel.b_ptr, perm, rel.b_seg = ops.csr_build(cols, rel.n_in, True)
+        rel.b_src, rel.b_w = rows[perm.long()].contiguous(), w[perm.long()].contiguous()
+        self.rel = rel
+
+    @classmethod
+    def of(cls, e_s, e_t, n_s, n_t, rank, world):
+        key = (e_s.data_ptr(), e_t.data_ptr(), e_s._version, e_t._version, n_s, n_t, rank, world)
+        hit = cls._cache.get(key)
+        if hit is None or hit[0] is not e_s or hit[1] is not e_t:
+            if len(cls._cache) > 16:
+                cls._cache.clear()
+            hit = (e_s, e_t, cls(e_s, e_t, n_s, n_t, rank, world))
+            cls._cache[key] = hit
+        return hit[2]
+
+
+def _pad_rows(x, n):
+    return x if x.size(0) == n else torch.cat([x, x.new_zeros(n - x.size(0), x.size(1))], dim=0)
+
+
+def sharded_relcnn(psi, x_gathered, sp, group):
+    """RelCNN.forward (rel.py:80-92) for this rank's nodes only.  x_gathered: the layer-0 features of
+    ALL nodes in the gathered layout [world * n_max, C]; returns [n_loc, out_channels]."""
+    own = torch.arange(sp.n_loc, device=x_gathered.device) + dist.get_rank(group) * sp.n_max
+    feats = [x_gathered[own]]
+    full = x_gathered
+    for i, conv in enumerate(psi.convs):
+        stacked = ops.rel_aggregate_op(full, sp.rel)                      # [n_loc, 3 C]
+        weight = torch.cat([conv.root.weight, conv.lin1.weight, conv.lin2.weight], dim=1)
+        h = ops.node_linear(stacked, weight, conv.root.bias, relu=True)    # [n_loc, C_out]
+        feats.append(h)
+        if i + 1 < len(psi.convs):
+            full = all_gather_rows(_pad_rows(h, sp.n_max), group)
+    out = torch.cat(feats, dim=-1) if psi.cat else feats[-1]
+    return ops.node_linear(out, psi.final.weight, psi.final.bias) if psi.lin else out
+
+
 class RowShardedDGMC(DGMC):
     """DGMC whose sparse correspondence path is sharded by source rows over `group` (default: the
     world group).  forward() returns this rank's rows only: sparse [n_local, N_t] tensors with
     `.__idx__`, `.__val__` and `.__rows__ = (lo, hi)`; `loss` / `acc` / `hits_at_k` take the GLOBAL
     ground truth `y` and reduce over all ranks."""
 
-    def __init__(self, psi_1, psi_2, num_steps, k, detach=False, group=None):
+    def __init__(self, psi_1, psi_2, num_steps, k, detach=False, group=None, shard_psi=True):
         super().__init__(psi_1, psi_2, num_steps, k=k, detach=detach)
         assert k >= 1, 'row sharding applies to the sparse variant (k >= 1)'
         self.group = group
+        self.shard_psi = shard_psi  # node-shard psi_2 (RelCNN) instead of running it replicated
 
     def _world(self):
         return dist.get_rank(self.group), dist.get_world_size(self.group)
@@ -81,6 +194,10 @@ class RowShardedDGMC(DGMC):
         num_steps = self.num_steps or 0
         merged = ops.MergedPair.of(self.psi_2, self.training, edge_index_s, edge_index_t,
                                    edge_attr_s, edge_attr_t, N_s, N_t)
+        from .rel import RelCNN
+        sp = None
+        if self.shard_psi and world > 1 and merged is not None and isinstance(self.psi_2, RelCNN):
+            sp = ShardedPair.of(edge_index_s, edge_index_t, N_s, N_t, rank, world)
 
         h_loc = h_s[lo:hi]
         S_idx = self.__top_k__(h_loc.unsqueeze(0), h_t.unsqueeze(0))  # [1, n_loc, k]
@@ -107,14 +224,20 @@ class RowShardedDGMC(DGMC):
             S = ops.softmax_k(S_hat)
             r_s = torch.randn((1, N_s, R_in), dtype=h_s.dtype, device=h_s.device).view(N_s, R_in)
             r_t = all_reduce_sum(ops.transport(S, r_s[lo:hi], cand), self.group)
+            if sp is not None:
+                # node-sharded psi_2: layer-0 features of every node in the gathered layout (local
+                # index_select: every rank holds r_s and the all-reduced r_t), then this rank's nodes
+                x0 = torch.cat([r_s, r_t], dim=0)[sp.src_of]
+                o_loc = sharded_relcnn(self.psi_2, x0, sp, self.group)             # [n_loc, R_out]
+                p_loc = ops.node_linear(o_loc, w1)
+                p_s_loc = p_loc[:sp.ns_loc] + b1
+                p_t = all_gather_rows(_pad_rows(p_loc[sp.ns_loc:], sp.nt_max), self.group)[sp.pos_t]
+                S_hat = ops.diff_mlp(S_hat, p_s_loc, p_t, w2, b2, cand)
+                continue
             if merged is not None:
                 o = self.psi_2(torch.cat([r_s, r_t], dim=0), merged.edge_index, merged.edge_attr)
                 p = ops.node_linear(o, w1)
                 p_s, p_t = p[:N_s] + b1, p[N_s:]
-            else:
-                o_s = self.psi_2(r_s, edge_index_s, edge_attr_s)
-                o_t = self.psi_2(r_t, edge_index_t, edge_attr_t)
-                p_s, p_t = ops.node_linear(o_s, w1, b1), ops.node_linear(o_t, w1)
             S_hat = ops.diff_mlp(S_hat, p_s[lo:hi], p_t, w2, b2, cand)
         S_L = ops.softmax_k(S_hat)
         S_idx = S_idx.view(n_loc, k)
@@ -123,8 +246,7 @@ class RowShardedDGMC(DGMC):
         coords = torch.stack([row.reshape(-1), S_idx.reshape(-1)], dim=0)
         outs = []
         for val in (S_0, S_L):
-            sp = torch.sparse_coo_tensor(coords, val.reshape(-1), torch.Size([n_loc, N_t]),
-                                         requires_grad=val.requires_grad, check_invariants=False)
+            sp = _sparse_coo(coords, val.reshape(-1), torch.Size([n_loc, N_t]))
             sp.__idx__, sp.__val__, sp.__rows__ = S_idx, val, (lo, hi)
             outs.append(sp)
         return outs[0], outs[1]

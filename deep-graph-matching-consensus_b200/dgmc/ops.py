@@ -111,6 +111,7 @@ class GraphCSR(object):
 class _RelOperator(object):
     def __init__(self, graph):
         n, dev = graph.num_nodes, graph.in_ptr.device
+        self.n_out = self.n_in = n
         src, dst = graph.src, graph.dst
         node = torch.arange(n, dtype=torch.int32, device=dev)
         rows = torch.cat([3 * node, 3 * dst + 1, 3 * src + 2])          # segment of A
@@ -400,29 +401,36 @@ class _RelAggregate(torch.autograd.Function):
     [3N, C] result IS the [N, 3C] operand of the layer GEMM.  Backward is A^T g with g viewed as
     [3N, C].  Both directions therefore cost one balanced segmented gather (+ its fix-up)."""
     @staticmethod
-    def forward(ctx, x, graph):
+    def forward(ctx, x, rel):
         x = _f32(x)
-        n, c = x.shape
-        rel = graph.rel
-        cat = torch.empty(n, 3 * c, dtype=torch.float32, device=x.device)
-        segment_gather(x, 3 * n, rel.f_src, ptr=rel.f_ptr, w=rel.f_w, out=cat.view(3 * n, c),
-                       seg_of=rel.f_seg)
-        ctx.graph = graph
+        c = x.size(1)
+        cat = torch.empty(rel.n_out, 3 * c, dtype=torch.float32, device=x.device)
+        segment_gather(x, 3 * rel.n_out, rel.f_src, ptr=rel.f_ptr, w=rel.f_w,
+                       out=cat.view(3 * rel.n_out, c), seg_of=rel.f_seg)
+        ctx.rel = rel
         return cat
 
     @staticmethod
     def backward(ctx, g):
-        rel = ctx.graph.rel
+        rel = ctx.rel
         g = _f32(g)
-        n, c = g.size(0), g.size(1) // 3
-        dx = segment_gather(g.view(3 * n, c), n, rel.b_src, ptr=rel.b_ptr, w=rel.b_w, seg_of=rel.b_seg)
+        c = g.size(1) // 3
+        dx = segment_gather(g.view(3 * rel.n_out, c), rel.n_in, rel.b_src, ptr=rel.b_ptr, w=rel.b_w,
+                            seg_of=rel.b_seg)
         return dx, None
 
 
 def rel_aggregate(x, graph):
     """-> [N, 3C] = [x | mean_{j->i} x_j | mean_{i->j} x_j]  (the two propagate calls of
     rel.py:27-30, taken BEFORE the linear maps: mean(lin(x_j)) == lin(mean(x_j)))."""
-    return _RelAggregate.apply(x, graph)
+    return _RelAggregate.apply(x, graph.rel)
+
+
+def rel_aggregate_op(x, rel):
+    """Same with an explicit aggregation operator `rel` ([3 n_out, n_in] sparse matrix: f_* its CSR,
+    b_* the CSR of its transpose) — used by the node-sharded backbone, whose operator maps the
+    all-gathered features to this rank's nodes."""
+    return _RelAggregate.apply(x, rel)
 
 
 class _NeighborSum(torch.autograd.Function):

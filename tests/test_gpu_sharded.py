@@ -38,32 +38,35 @@ def _worker(rank, world, port, out):
             m = cls(RelCNN(32, 48, 2, dropout=0.0), RelCNN(16, 16, 2), num_steps=3, k=6).cuda().train()
             return m
 
-        single, sharded = build(DGMC), build(RowShardedDGMC)
+        single = build(DGMC)
         torch.manual_seed(123)
         _, S1 = single(x_s, e_s, None, None, x_t, e_t, None, None, y)
         l1 = single.loss(S1, y)
         l1.backward()
-        torch.manual_seed(123)
-        _, S2 = sharded(x_s, e_s, None, None, x_t, e_t, None, None, y)
-        share = sharded.loss(S2, y)
-        share.backward()
-        sharded.sync_gradients()
-        lo, hi = S2.__rows__
-        assert torch.equal(S2.__idx__, S1.__idx__[lo:hi]), 'candidate sets differ'
-        ref = S1.__val__[lo:hi]
-        assert (S2.__val__ - ref).abs().max().item() <= 1e-5 * ref.abs().max().item() + 1e-7
-        assert abs(sharded.global_loss(share).item() - l1.item()) <= 1e-5 * abs(l1.item()) + 1e-7
-        assert sharded.acc(S2, y) == pytest.approx(single.acc(S1, y))
-        assert sharded.hits_at_k(3, S2, y) == pytest.approx(single.hits_at_k(3, S1, y))
-        # psi_2.final.bias cancels in o_s - o_t: its true gradient is 0 and what is computed is
-        # rounding noise, hence the floor relative to the largest gradient of the whole model
         floor = 1e-5 * max(p.grad.abs().max().item() for p in single.parameters() if p.grad is not None)
-        for (n, p), q in zip(single.named_parameters(), sharded.parameters()):
-            if p.grad is None:
-                assert q.grad is None
-                continue
-            scale = p.grad.abs().max().item()
-            assert (p.grad - q.grad).abs().max().item() <= 5e-4 * scale + floor, n
+        for shard_psi in (False, True):   # psi_2 replicated / node-sharded with all-gathers
+            sharded = build(RowShardedDGMC)
+            sharded.shard_psi = shard_psi
+            torch.manual_seed(123)
+            _, S2 = sharded(x_s, e_s, None, None, x_t, e_t, None, None, y)
+            share = sharded.loss(S2, y)
+            share.backward()
+            sharded.sync_gradients()
+            lo, hi = S2.__rows__
+            assert torch.equal(S2.__idx__, S1.__idx__[lo:hi]), 'candidate sets differ'
+            ref = S1.__val__[lo:hi]
+            assert (S2.__val__ - ref).abs().max().item() <= 1e-5 * ref.abs().max().item() + 1e-7
+            assert abs(sharded.global_loss(share).item() - l1.item()) <= 1e-5 * abs(l1.item()) + 1e-7
+            assert sharded.acc(S2, y) == pytest.approx(single.acc(S1, y))
+            assert sharded.hits_at_k(3, S2, y) == pytest.approx(single.hits_at_k(3, S1, y))
+            # psi_2.final.bias cancels in o_s - o_t: its true gradient is 0 and what is computed is
+            # rounding noise, hence the floor relative to the largest gradient of the whole model
+            for (n, p), q in zip(single.named_parameters(), sharded.parameters()):
+                if p.grad is None:
+                    assert q.grad is None
+                    continue
+                scale = p.grad.abs().max().item()
+                assert (p.grad - q.grad).abs().max().item() <= 5e-4 * scale + floor, (shard_psi, n)
         out.put((rank, 'ok'))
     except Exception:  # pragma: no cover
         import traceback
