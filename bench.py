@@ -152,14 +152,15 @@ def cpu_reference_steps(w, inputs, steps, warmup, budget_s):
     t0 = time.perf_counter()
     one_step()  # warm-up (also sizes the sample)
     first = time.perf_counter() - t0
-    for _ in range(max(0, min(warmup - 1, int(budget_s * 0.2 / max(first, 1e-3))))):
+    extra = max(0, min(warmup - 1, int(budget_s * 0.2 / max(first, 1e-3))))
+    for _ in range(extra):
         one_step()
     n = max(1, min(steps, int(budget_s * 0.8 / max(first, 1e-3))))
     t0 = time.perf_counter()
     for _ in range(n):
         one_step()
     dt = (time.perf_counter() - t0) / n
-    return 1.0 / dt, n, cores, dt
+    return 1.0 / dt, n, cores, dt, 1 + extra
 
 
 # ------------------------------------------------------------------------------------------------
@@ -334,12 +335,12 @@ def main():
             return 0
         inputs = make_inputs(w)
         budget = args.cpu_budget or 150.0
-        sps, n, cores, dt = cpu_reference_steps(w, inputs, args.steps, args.warmup, budget)
+        sps, n, cores, dt, wu = cpu_reference_steps(w, inputs, args.steps, args.warmup, budget)
         sample = ('%d full steps of the same workload (oracle port of the reference: torch CPU '
                   'ops, row-chunked matmul+topk for __top_k__), %d threads' % (n, cores))
         emit({
             'impl': 'reference', 'metric': METRIC, 'value': sps, 'unit': 'steps/s', 'n_gpus': 0,
-            'steps': n, 'warmup': 1, 'ms_per_step': dt * 1e3, 'higher_is_better': True,
+            'steps': n, 'warmup': wu, 'ms_per_step': dt * 1e3, 'higher_is_better': True,
             'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
             'config': config,
             'cpu_baseline': {'value': sps, 'unit': 'steps/s', 'cores': cores, 'kind': 'port',
@@ -486,7 +487,7 @@ def main():
             'roofline': roofline, 'roofline_all': rl,
         }
         if world == 1 and not args.no_cpu_baseline and not args.nodes:
-            sps, n, cores, dt = cpu_reference_steps(w, host, 2, 1, args.cpu_budget or 30.0)
+            sps, n, cores, dt, _ = cpu_reference_steps(w, host, 2, 1, args.cpu_budget or 30.0)
             out['cpu_baseline'] = {
                 'value': sps, 'unit': 'steps/s', 'cores': cores, 'kind': 'port',
                 'sample': '%d full step(s) of the same workload after 1 warm-up, oracle port of the '
