@@ -50,6 +50,23 @@ def parse_header(path=HEADER_PATH):
     return protos
 
 
+def _try_build():
+    """The shared library is built in-tree by __graft_entry__.build(); if it is absent (fresh
+    checkout) and nvcc is available, build it now.  This compiles the extension — it is not a
+    fallback path: without the library the import fails."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location('dgmc_b200_build', os.path.join(PKG_ROOT, 'build.py'))
+    mod = importlib.util.module_from_spec(spec)
+    try:
+        spec.loader.exec_module(mod)
+        mod.build()
+    except Exception as exc:  # pragma: no cover
+        raise ImportError('dgmc (B200): could not build %s: %s' % (LIB_PATH, exc))
+
+
+if not os.path.exists(LIB_PATH) and 'DGMC_B200_LIB' not in os.environ:
+    _try_build()
+
 if not os.path.exists(LIB_PATH):
     raise ImportError(
         'dgmc (B200): %s not found. Build it with `python -c "import __graft_entry__ as g; '
