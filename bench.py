@@ -267,6 +267,58 @@ def kernel_rooflines(w, model, e_t, peaks, step_ms, iters=5):
     return rows
 
 
+def pascal_step_bench(dev, steps, warmup):
+    """`--pascal`: BASELINE.json configs[1] — PascalVOC-keypoint-shaped synthetic batch (512 graph
+    pairs of 10-20 nodes, 1024-d features, 2-d pseudo-coordinates, SplineCNN psi_1 1024->256 L2 /
+    psi_2 128->128 L2, dense S, 10 consensus steps, examples/pascal.py:46-76).  A parity-test
+    configuration, timed here for the record (not the headline metric)."""
+    from dgmc.models import DGMC, SplineCNN
+    g = torch.Generator().manual_seed(2)
+    B = 512
+
+    def batch(sizes):
+        xs, es, ats, bs, off = [], [], [], [], 0
+        for i, n in enumerate(sizes):
+            xs.append(torch.randn(n, 1024, generator=g))
+            es.append(torch.randint(n, (2, 5 * n), generator=g) + off)
+            ats.append(torch.rand(5 * n, 2, generator=g))
+            bs.append(torch.full((n, ), i, dtype=torch.long))
+            off += n
+        return [t.to(dev) for t in (torch.cat(xs), torch.cat(es, 1), torch.cat(ats), torch.cat(bs))]
+
+    sizes = torch.randint(10, 21, (B, ), generator=g).tolist()
+    x_s, e_s, a_s, b_s = batch(sizes)
+    x_t, e_t, a_t, b_t = batch(sizes)
+    y = torch.stack([torch.arange(x_s.size(0)), torch.cat([torch.randperm(n, generator=g) for n in sizes])]).to(dev)
+    torch.manual_seed(0)
+    model = DGMC(SplineCNN(1024, 256, 2, 2, cat=False, dropout=0.5), SplineCNN(128, 128, 2, 2, cat=True),
+                 num_steps=10).to(dev).train()
+    opt = torch.optim.Adam(model.parameters(), lr=1e-3)
+
+    def step():
+        opt.zero_grad(set_to_none=True)
+        S_0, S_L = model(x_s, e_s, a_s, b_s, x_t, e_t, a_t, b_t)
+        loss = model.loss(S_0, y) + model.loss(S_L, y)
+        loss.backward()
+        opt.step()
+        return loss
+
+    for _ in range(warmup):
+        step()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(steps):
+        loss = step()
+    b.record()
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(b) / steps
+    emit({'pascal_shaped': {'graph_pairs': B, 'nodes': int(x_s.size(0)), 'edges': int(e_s.size(1)),
+                            'ms_per_step': ms, 'steps_per_s': 1e3 / ms, 'pairs_per_s': B * 1e3 / ms,
+                            'loss': loss.item(), 'execution': 'eager (batch sizes vary per step in '
+                            'the reference scripts, so no graph capture)'}})
+
+
 def scale_kernels(n, dev):
     """`--scale-kernels N`: the hot kernels alone on an N x N-node synthetic pair (BASELINE.json
     configs[4] shape at N = 1,000,000: 256-d embeddings, R = 64, k_eff = 20, 5 out-edges per node),
@@ -307,6 +359,7 @@ def main():
     ap.add_argument('--nodes', type=int, default=0, metavar='N',
                     help='scaling study: replace the DBP15K shape by an N x N-node pair (5 edges per '
                          'node, N/4 train pairs); not the headline configuration')
+    ap.add_argument('--pascal', action='store_true', help='time the PascalVOC-shaped dense config and exit')
     ap.add_argument('--scale-kernels', type=int, default=0, metavar='N',
                     help='time the hot kernels alone on an N x N-node pair and exit')
     ap.add_argument('--profile-eager', action='store_true',
@@ -354,6 +407,9 @@ def main():
     dev = torch.device('cuda', local)
     if args.scale_kernels:
         scale_kernels(args.scale_kernels, dev)
+        return 0
+    if args.pascal:
+        pascal_step_bench(dev, args.steps, args.warmup)
         return 0
     if world > 1:
         os.environ.setdefault('TORCH_NCCL_ASYNC_ERROR_HANDLING', '0')  # collectives get graph-captured
