@@ -479,6 +479,20 @@ def main():
     ms_per_step = ms.item() / args.steps
     value = 1e3 / ms_per_step  # one job: with N > 1 the source rows are sharded over the ranks
 
+    if os.environ.get('DGMC_BENCH_KINETO'):
+        # per-kernel device time of graph replays (warm caches, real overlap), via CUPTI
+        from torch.profiler import ProfilerActivity, profile
+        with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
+            for _ in range(5):
+                graphed(*args_of(d))
+            torch.cuda.synchronize()
+        rows = [(e.key, e.count, e.device_time_total) for e in prof.key_averages() if e.device_time_total > 0]
+        rows.sort(key=lambda r: -r[2])
+        tot = sum(r[2] for r in rows)
+        print('kernel time per replay: %.3f ms over %d kernel names' % (tot / 5e3, len(rows)), file=sys.stderr)
+        for name, cnt, t in rows[:40]:
+            print('%8.1f us/replay %5d x  %s' % (t / 5, cnt // 5, name[:110]), file=sys.stderr)
+
     # ---- end-to-end: pinned host inputs copied every step (graph structure rebuilt inside the
     #      captured step), loss read back --------------------------------------------------------
     h2d = sum(v.numel() * v.element_size() for v in pinned.values())

@@ -105,21 +105,35 @@ __global__ void __launch_bounds__(WG_THREADS) wgrad_partial_kernel(
         partial_b[(size_t)split * M + m0 + tid] = bsum;
 }
 
+// one warp per output element: lanes stride over the partial tiles (coalesced across the warps of a
+// block, which own consecutive elements), fixed shuffle tree -> deterministic
 __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* __restrict__ partial,
                                                            const float* __restrict__ partial_b, int splits,
                                                            int MN, int M, float* __restrict__ dw,
                                                            float* __restrict__ db) {
     const int total = MN + (db ? M : 0);
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int lane = threadIdx.x & 31;
+    // block = 8 warps x 32 lanes handles 32 consecutive elements: lane l of warp w reads element
+    // (base + l) of partial tiles w, w + 8, ...  -> 128-byte coalesced rows; then a shared-memory
+    // transpose-free reduction over the 8 warps.
+    __shared__ float red[8][33];
+    for (int base = blockIdx.x * 32; base < total; base += gridDim.x * 32) {
+        const int i = base + lane;
+        const int w = threadIdx.x >> 5;
         float s = 0.f;
-        if (i < MN) {
-            for (int p = 0; p < splits; ++p) s += partial[(size_t)p * MN + i];
-            dw[i] = s;
-        } else {
-            const int m = i - MN;
-            for (int p = 0; p < splits; ++p) s += partial_b[(size_t)p * M + m];
-            db[m] = s;
+        if (i < total) {
+            if (i < MN) for (int p = w; p < splits; p += 8) s += partial[(size_t)p * MN + i];
+            else        for (int p = w; p < splits; p += 8) s += partial_b[(size_t)p * M + (i - MN)];
         }
+        red[w][lane] = s;
+        __syncthreads();
+        if (w == 0 && i < total) {
+            float t = 0.f;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) t += red[q][lane];
+            if (i < MN) dw[i] = t; else db[i - MN] = t;
+        }
+        __syncthreads();
     }
 }
 
@@ -136,6 +150,29 @@ static int wgrad_splits(long long K, int M, int N) {
 }  // namespace dgmc
 
 using namespace dgmc;
+
+// ---- two-stage interface: several partial launches (e.g. one per consensus step, all for the same
+// weight) can share ONE reduction -------------------------------------------------------------------
+extern "C" int dgmc_wgrad_splits(int64_t k, int m, int n) { return wgrad_splits(k, m, n); }
+
+extern "C" int dgmc_wgrad_partial(const float* g, int64_t ldg, const float* x, int64_t ldx, int64_t k, int m,
+                                  int n, float* partial, float* partial_b, dgmc_stream_t stream) {
+    DGMC_REQUIRE(g && x && partial && k >= 0 && m >= 1 && n >= 1 && ldg >= m && ldx >= n,
+                 "wgrad_partial: bad arguments (k=%lld m=%d n=%d)", (long long)k, m, n);
+    const int splits = wgrad_splits(k, m, n);
+    dim3 grid((n + WG_TN - 1) / WG_TN, (m + WG_TM - 1) / WG_TM, splits);
+    wgrad_partial_kernel<<<grid, WG_THREADS, 0, stream>>>(g, ldg, x, ldx, k, m, n, splits, partial, partial_b);
+    return check_launch("wgrad_partial");
+}
+
+extern "C" int dgmc_wgrad_reduce(const float* partial, const float* partial_b, int n_partials, int m, int n,
+                                 float* dw, float* db, dgmc_stream_t stream) {
+    DGMC_REQUIRE(partial && dw && n_partials >= 1 && m >= 1 && n >= 1 && (!db || partial_b),
+                 "wgrad_reduce: bad arguments");
+    const int total = m * n + (db ? m : 0);
+    wgrad_reduce_kernel<<<(total + 31) / 32, 256, 0, stream>>>(partial, partial_b, n_partials, m * n, m, dw, db);
+    return check_launch("wgrad_reduce");
+}
 
 extern "C" size_t dgmc_wgrad_workspace(int64_t k, int m, int n) {
     const int splits = wgrad_splits(k, m, n);
@@ -158,6 +195,6 @@ extern "C" int dgmc_wgrad(const float* g, int64_t ldg, const float* x, int64_t l
     wgrad_partial_kernel<<<grid, WG_THREADS, 0, stream>>>(g, ldg, x, ldx, k, m, n, splits, partial,
                                                          db ? partial_b : nullptr);
     const int total = m * n + (db ? m : 0);
-    wgrad_reduce_kernel<<<(total + 255) / 256, 256, 0, stream>>>(partial, partial_b, splits, m * n, m, dw, db);
+    wgrad_reduce_kernel<<<(total + 31) / 32, 256, 0, stream>>>(partial, partial_b, splits, m * n, m, dw, db);
     return check_launch("wgrad", 2);
 }

@@ -132,6 +132,14 @@ class DGMC(torch.nn.Module):
 
     def forward(self, x_s, edge_index_s, edge_attr_s, batch_s, x_t, edge_index_t, edge_attr_t,
                 batch_t, y=None):
+        # psi_2 and the consensus MLP are applied num_steps times with the same weights: their
+        # weight gradients are reduced once per backward pass (ops.WGradGroup)
+        with ops.deferred_wgrad():
+            return self._forward(x_s, edge_index_s, edge_attr_s, batch_s, x_t, edge_index_t,
+                                 edge_attr_t, batch_t, y)
+
+    def _forward(self, x_s, edge_index_s, edge_attr_s, batch_s, x_t, edge_index_t, edge_attr_t,
+                 batch_t, y=None):
         """-> (S_0, S_L): dense [sum N_s, N_t] tensors for k < 1, else un-coalesced sparse COO
         tensors carrying `.__idx__` [sum N_s, k_eff] int64 and `.__val__` [sum N_s, k_eff]
         (gradients flow through `__val__`), exactly as dgmc.py:114-244."""
@@ -158,13 +166,14 @@ class DGMC(torch.nn.Module):
                 # psi_2 shares its weights between the two graphs: run it ONCE on their disjoint
                 # union (same arithmetic per node, half the launches, twice the GEMM height)
                 o = self.psi_2(torch.cat([r_s, r_t], dim=0), merged.edge_index, merged.edge_attr)
-                p = ops.node_linear(o, w1)
+                p = ops.node_linear(o, w1, key=('mlp0', id(self)))
                 p_s, p_t = p[:r_s.size(0)] + b1, p[r_s.size(0):]
                 return _repad(p_s, s_mask), _repad(p_t, t_mask)
             o_s = self.psi_2(r_s, edge_index_s, edge_attr_s)
             o_t = self.psi_2(r_t, edge_index_t, edge_attr_t)
             o_s, o_t = _repad(o_s, s_mask), _repad(o_t, t_mask)
-            return ops.node_linear(o_s, w1, b1), ops.node_linear(o_t, w1)
+            return (ops.node_linear(o_s, w1, b1, key=('mlp0s', id(self))),
+                    ops.node_linear(o_t, w1, key=('mlp0t', id(self))))
 
         if self.k < 1:
             # ------ dense variant (dgmc.py:161-183) ------

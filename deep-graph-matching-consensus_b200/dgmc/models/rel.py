@@ -31,7 +31,7 @@ class RelConv(torch.nn.Module):
         graph = ops.GraphCSR.of(edge_index, x.size(0))
         stacked = ops.rel_aggregate(x, graph)  # [N, 3 C_in] = [x | mean_in | mean_out]
         weight = torch.cat([self.root.weight, self.lin1.weight, self.lin2.weight], dim=1)
-        return ops.node_linear(stacked, weight, self.root.bias, relu=relu)
+        return ops.node_linear(stacked, weight, self.root.bias, relu=relu, key=('relconv', id(self)))
 
     def __repr__(self):
         return '{}({}, {})'.format(type(self).__name__, self.in_channels, self.out_channels)
@@ -72,7 +72,8 @@ class RelCNN(torch.nn.Module):
                 h = norm(h)
             feats.append(F.dropout(h, p=self.dropout, training=self.training))
         out = torch.cat(feats, dim=-1) if self.cat else feats[-1]
-        return ops.node_linear(out, self.final.weight, self.final.bias) if self.lin else out
+        return ops.node_linear(out, self.final.weight, self.final.bias, key=('final', id(self))) \
+            if self.lin else out
 
     def __repr__(self):
         return ('{}({}, {}, num_layers={}, batch_norm={}, cat={}, lin={}, dropout={})').format(

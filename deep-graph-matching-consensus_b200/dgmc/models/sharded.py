@@ -155,12 +155,12 @@ def sharded_relcnn(psi, x_gathered, sp, group):
     for i, conv in enumerate(psi.convs):
         stacked = ops.rel_aggregate_op(full, sp.rel)                      # [n_loc, 3 C]
         weight = torch.cat([conv.root.weight, conv.lin1.weight, conv.lin2.weight], dim=1)
-        h = ops.node_linear(stacked, weight, conv.root.bias, relu=True)    # [n_loc, C_out]
+        h = ops.node_linear(stacked, weight, conv.root.bias, relu=True, key=('relconv', id(conv)))
         feats.append(h)
         if i + 1 < len(psi.convs):
             full = all_gather_rows(_pad_rows(h, sp.n_max), group)
     out = torch.cat(feats, dim=-1) if psi.cat else feats[-1]
-    return ops.node_linear(out, psi.final.weight, psi.final.bias) if psi.lin else out
+    return ops.node_linear(out, psi.final.weight, psi.final.bias, key=('final', id(psi))) if psi.lin else out
 
 
 class RowShardedDGMC(DGMC):
@@ -178,8 +178,8 @@ class RowShardedDGMC(DGMC):
     def _world(self):
         return dist.get_rank(self.group), dist.get_world_size(self.group)
 
-    def forward(self, x_s, edge_index_s, edge_attr_s, batch_s, x_t, edge_index_t, edge_attr_t,
-                batch_t, y=None):
+    def _forward(self, x_s, edge_index_s, edge_attr_s, batch_s, x_t, edge_index_t, edge_attr_t,
+                 batch_t, y=None):
         assert batch_s is None and batch_t is None, 'row sharding handles one graph pair'
         rank, world = self._world()
         h_s = self.psi_1(x_s, edge_index_s, edge_attr_s)
@@ -229,14 +229,14 @@ class RowShardedDGMC(DGMC):
                 # index_select: every rank holds r_s and the all-reduced r_t), then this rank's nodes
                 x0 = torch.cat([r_s, r_t], dim=0)[sp.src_of]
                 o_loc = sharded_relcnn(self.psi_2, x0, sp, self.group)             # [n_loc, R_out]
-                p_loc = ops.node_linear(o_loc, w1)
+                p_loc = ops.node_linear(o_loc, w1, key=('mlp0', id(self)))
                 p_s_loc = p_loc[:sp.ns_loc] + b1
                 p_t = all_gather_rows(_pad_rows(p_loc[sp.ns_loc:], sp.nt_max), self.group)[sp.pos_t]
                 S_hat = ops.diff_mlp(S_hat, p_s_loc, p_t, w2, b2, cand)
                 continue
             if merged is not None:
                 o = self.psi_2(torch.cat([r_s, r_t], dim=0), merged.edge_index, merged.edge_attr)
-                p = ops.node_linear(o, w1)
+                p = ops.node_linear(o, w1, key=('mlp0', id(self)))
                 p_s, p_t = p[:N_s] + b1, p[N_s:]
             S_hat = ops.diff_mlp(S_hat, p_s[lo:hi], p_t, w2, b2, cand)
         S_L = ops.softmax_k(S_hat)

@@ -348,23 +348,53 @@ def diff_mlp(s_hat, ps, pt, w2, b2, cand):
 # --------------------------------------------------------------------------------------------
 # per-node linear map with a split-K weight gradient
 # --------------------------------------------------------------------------------------------
+class WGradGroup(object):
+    """All applications of ONE weight inside one forward pass (the consensus loop applies psi_2 and
+    the MLP num_steps times).  Their backward passes each write partial tiles into a shared buffer;
+    only the LAST one to run reduces them and hands autograd the summed gradient — the others
+    return None (= no contribution), so every parameter receives one gradient per step instead
+    of num_steps, and one reduction kernel instead of num_steps."""
+    def __init__(self):
+        self.calls = 0          # forward applications
+        self.done = 0           # backward passes seen
+        self.partial = self.partial_b = None
+        self.splits = 0
+
+
+_DEFER = [None]  # {key: WGradGroup} while a deferred-wgrad region is active
+
+
+class deferred_wgrad(object):
+    """Context manager around a region that applies the same Linear maps repeatedly and whose
+    every application takes part in the backward pass."""
+    def __enter__(self):
+        self.prev, _DEFER[0] = _DEFER[0], {}
+        return self
+
+    def __exit__(self, *exc):
+        _DEFER[0] = self.prev
+
+
 class _NodeLinear(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, relu):
+    def forward(ctx, x, weight, bias, relu, group):
         if relu:  # bias + ReLU in the library GEMM's epilogue
             y = torch._addmm_activation(bias, x, weight.t(), use_gelu=False)
             ctx.save_for_backward(x, weight, y)
         else:
             y = torch.addmm(bias, x, weight.t()) if bias is not None else x @ weight.t()
             ctx.save_for_backward(x, weight)
-        ctx.has_bias, ctx.relu = bias is not None, relu
+        ctx.has_bias, ctx.relu, ctx.group = bias is not None, relu, group
+        if group is not None:
+            ctx.slot = group.calls
+            group.calls += 1
         return y
 
     @staticmethod
     def backward(ctx, g):
         if ctx.relu:
             x, weight, y = ctx.saved_tensors
-            g = g * (y > 0)
+            g = torch.ops.aten.threshold_backward(g, y, 0)  # g * (y > 0) in one kernel
         else:
             x, weight = ctx.saved_tensors
         g = _f32(g)
@@ -372,22 +402,46 @@ class _NodeLinear(torch.autograd.Function):
         dx = g @ weight if ctx.needs_input_grad[0] else None
         dw = db = None
         if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
-            dw = torch.empty_like(weight)
-            db = torch.empty(m, dtype=torch.float32, device=g.device) if ctx.has_bias else None
-            ws = _workspace(query('dgmc_wgrad_workspace', k, m, n), g.device)
-            call('dgmc_wgrad', g, g.stride(0), RowStrided(x), x.stride(0), k, m, n, dw, db, ws,
-                 ws.numel(), stream_ptr())
-        return dx, dw, db, None
+            grp = ctx.group
+            if grp is None:
+                dw = torch.empty_like(weight)
+                db = torch.empty(m, dtype=torch.float32, device=g.device) if ctx.has_bias else None
+                ws = _workspace(query('dgmc_wgrad_workspace', k, m, n), g.device)
+                call('dgmc_wgrad', g, g.stride(0), RowStrided(x), x.stride(0), k, m, n, dw, db, ws,
+                     ws.numel(), stream_ptr())
+            else:
+                if grp.partial is None:
+                    grp.splits = query('dgmc_wgrad_splits', k, m, n)
+                    grp.partial = torch.empty(grp.calls * grp.splits, m * n, dtype=torch.float32,
+                                              device=g.device)
+                    grp.partial_b = torch.empty(grp.calls * grp.splits, m, dtype=torch.float32,
+                                                device=g.device) if ctx.has_bias else None
+                off = ctx.slot * grp.splits
+                call('dgmc_wgrad_partial', g, g.stride(0), RowStrided(x), x.stride(0), k, m, n,
+                     grp.partial[off:off + grp.splits],
+                     None if grp.partial_b is None else grp.partial_b[off:off + grp.splits], stream_ptr())
+                grp.done += 1
+                if grp.done == grp.calls:  # last backward of this weight: reduce everything once
+                    dw = torch.empty_like(weight)
+                    db = torch.empty(m, dtype=torch.float32, device=g.device) if ctx.has_bias else None
+                    call('dgmc_wgrad_reduce', grp.partial, grp.partial_b, grp.calls * grp.splits, m, n,
+                         dw, db, stream_ptr())
+                    grp.partial = grp.partial_b = None
+                    grp.done = 0  # a second backward over a retained graph starts afresh
+        return dx, dw, db, None, None
 
 
-def node_linear(x, weight, bias=None, relu=False):
+def node_linear(x, weight, bias=None, relu=False, key=None):
     """relu?(x [nodes, in] @ weight[out, in]^T + bias): library GEMM forward (bias and ReLU in its
     epilogue) and input gradient; the weight / bias gradient (a reduction over all nodes with a tiny
     output) runs on the split-K kernel dgmc_wgrad when the output is small, else stays with the
     library."""
     if weight.size(0) * weight.size(1) <= 64 * 1024 and x.size(0) >= 2048 and x.is_cuda \
             and x.dtype == torch.float32 and x.stride(1) == 1 and (bias is not None or not relu):
-        return _NodeLinear.apply(x, weight, bias, relu)
+        group = None
+        if key is not None and _DEFER[0] is not None and torch.is_grad_enabled():
+            group = _DEFER[0].setdefault((key, x.size(0), tuple(weight.shape)), WGradGroup())
+        return _NodeLinear.apply(x, weight, bias, relu, group)
     y = torch.nn.functional.linear(x, weight, bias)
     return torch.relu(y) if relu else y
 

@@ -185,6 +185,16 @@ int dgmc_spline_gather_bwd(const float* g, int64_t ldg, const int32_t* out_ptr,
  * the node count k is large and m x n is small: a library SGEMM tiles only the 64 x 192 output and
  * runs on 3 CTAs; this kernel splits the node dimension over the whole chip.  fp32, deterministic. */
 size_t dgmc_wgrad_workspace(int64_t k, int m, int n);
+/* Two-stage form: dgmc_wgrad_partial writes dgmc_wgrad_splits(k, m, n) partial tiles
+ * (partial [splits, m, n], partial_b [splits, m], partial_b may be NULL); dgmc_wgrad_reduce adds
+ * n_partials consecutive tiles.  Lets the backward passes of all consensus steps, which share their
+ * weights (dgmc.py:204-223 calls psi_2 and the MLP num_steps times), pay for one reduction and hand
+ * autograd one gradient per parameter instead of num_steps. */
+int dgmc_wgrad_splits(int64_t k, int m, int n);
+int dgmc_wgrad_partial(const float* g, int64_t ldg, const float* x, int64_t ldx, int64_t k, int m, int n,
+                       float* partial, float* partial_b, dgmc_stream_t stream);
+int dgmc_wgrad_reduce(const float* partial, const float* partial_b, int n_partials, int m, int n,
+                      float* dw, float* db, dgmc_stream_t stream);
 int dgmc_wgrad(const float* g, int64_t ldg, const float* x, int64_t ldx, int64_t k, int m, int n,
                float* dw, float* db, void* workspace, size_t workspace_bytes, dgmc_stream_t stream);
 

@@ -51,13 +51,17 @@ def test_dbp15k_lite_sparse_training_step_against_oracle():
     with replay_draws(draws, 'cuda'):
         S_0, S_L = model(dev[0], dev[1], None, None, dev[2], dev[3], None, None, dev[4])
     loss = model.loss(S_L, dev[4])
+    loss.backward()   # 4,000+ nodes: goes through the grouped split-K weight-gradient path
 
     def oracle(dtype, S_idx=None):
-        p = {n: v.to(dtype) for n, v in params.items()}
+        p = {n: v.to(dtype).requires_grad_() for n, v in params.items()}
         out = O.dgmc_forward(s1, s2, p, x_s.to(dtype), e_s, None, None, x_t.to(dtype), e_t, None, None,
                              steps, k, y=y, training=True, draws=draws, topk_dtype=torch.float64,
                              S_idx=S_idx)
         out['loss'] = O.loss(out['S_L'], y, idx=out['idx'])
+        out['loss'].backward()
+        out['grads'] = {n: v.grad for n, v in p.items()}
+        out = {n: (v.detach() if torch.is_tensor(v) else v) for n, v in out.items()}
         return out
 
     ref64 = oracle(torch.float64)
@@ -72,6 +76,14 @@ def test_dbp15k_lite_sparse_training_step_against_oracle():
     assert_parity(gL[same], rL[same], qL[same], what='S_L')
     if bool(same.all()):
         assert_parity(loss, ref64['loss'], ref32['loss'], what='loss')
+        got = dict(model.named_parameters())
+        for n, gref in ref64['grads'].items():
+            if gref is None:
+                continue
+            scale = gref.abs().max().item()
+            noise = (ref32['grads'][n].double() - gref).abs().max().item()
+            err = (got[n].grad.double().cpu() - gref).abs().max().item()
+            assert err <= max(5e-4 * scale, 5 * noise) + 1e-9, (n, err, scale, noise)
 
 
 def test_pascal_shaped_ragged_dense_batch_against_oracle():
