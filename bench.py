@@ -206,6 +206,15 @@ def timed(fn, iters, flush=None):
     return total / iters
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from the `ncu --set full` captures under
+# profiles/ (DBP15K shape only; None where the captured launch is not the one timed here)
+NCU_TRAFFIC_DBP15K = {
+    'K1': 19.98e6 + 47.37e6,  # topk_tc_kernel + topk_merge_kernel (r1f/r1j captures; the two cast
+                              # kernels, 40 MB fp32 in / 20 MB bf16 out, were not captured)
+    'K6': 13.08e6,            # diff_mlp_fwd_kernel<16,1> (r1f capture)
+}
+
+
 def kernel_rooflines(w, model, e_t, peaks, step_ms, iters=5):
     """Times each hot kernel alone (cold L2) on step-shaped data.  Algorithmic bytes / flops per
     launch follow SURVEY.md §8(d): `bytes_min` (every operand read once, every result written once)
@@ -237,13 +246,16 @@ def kernel_rooflines(w, model, e_t, peaks, step_ms, iters=5):
     def pick(table_bytes, b_min, b_logical):
         return (b_logical, 'logical') if table_bytes > l2 else (b_min, 'min')
 
+    dbp15k = (n_s, n_t, C, R) == (19388, 19572, 256, 64)
+
     def add(name, fn, calls, work, bound, basis=''):
         ms = timed(fn, iters, flush)
+        traffic = NCU_TRAFFIC_DBP15K.get(name[:2]) if dbp15k else None
         achieved = work / (ms * 1e-3) / (1e12 if bound == 'tensor' else 1e9)
         peak = tf if bound == 'tensor' else hbm
         rows.append({'kernel': name, 'bound': bound, 'achieved': round(achieved, 2), 'peak': peak,
                      'unit': 'TFLOP/s' if bound == 'tensor' else 'GB/s',
-                     'frac': round(achieved / peak, 4), 'traffic': None, 'work_basis': basis,
+                     'frac': round(achieved / peak, 4), 'traffic': traffic, 'work_basis': basis,
                      'ms_per_launch': round(ms, 4), 'launches_per_step': calls,
                      'share_of_step': round(ms * calls / step_ms, 4) if step_ms else None})
 
