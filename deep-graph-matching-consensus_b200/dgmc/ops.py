@@ -348,6 +348,9 @@ def diff_mlp(s_hat, ps, pt, w2, b2, cand):
 # --------------------------------------------------------------------------------------------
 # per-node linear map with a split-K weight gradient
 # --------------------------------------------------------------------------------------------
+WGRAD_TENSOR_CORE = False
+
+
 class WGradGroup(object):
     """All applications of ONE weight inside one forward pass (the consensus loop applies psi_2 and
     the MLP num_steps times).  Their backward passes each write partial tiles into a shared buffer;
@@ -403,31 +406,32 @@ class _NodeLinear(torch.autograd.Function):
         dw = db = None
         if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
             grp = ctx.group
-            if grp is None:
+            # fp32 FFMA split-K kernel by default; WGRAD_TENSOR_CORE switches to the tcgen05 3xTF32
+            # kernel (correct, but staging-bound and 2x slower at these skinny shapes: DESIGN.md §8)
+            tc = WGRAD_TENSOR_CORE and bool(query('dgmc_wgrad_tc_supported', m, n))
+            fn_splits = 'dgmc_wgrad_tc_splits' if tc else 'dgmc_wgrad_splits'
+            fn_partial = 'dgmc_wgrad_tc_partial' if tc else 'dgmc_wgrad_partial'
+            calls, slot = (1, 0) if grp is None else (grp.calls, ctx.slot)
+            holder = grp if grp is not None else WGradGroup()
+            if holder.partial is None:
+                holder.splits = query(fn_splits, k, m, n)
+                holder.partial = torch.empty(calls * holder.splits, m * n, dtype=torch.float32,
+                                             device=g.device)
+                holder.partial_b = torch.empty(calls * holder.splits, m, dtype=torch.float32,
+                                               device=g.device) if ctx.has_bias else None
+            off = slot * holder.splits
+            call(fn_partial, g, g.stride(0), RowStrided(x), x.stride(0), k, m, n,
+                 holder.partial[off:off + holder.splits],
+                 None if holder.partial_b is None else holder.partial_b[off:off + holder.splits],
+                 stream_ptr())
+            holder.done += 1
+            if holder.done == calls:  # last backward of this weight: reduce everything once
                 dw = torch.empty_like(weight)
                 db = torch.empty(m, dtype=torch.float32, device=g.device) if ctx.has_bias else None
-                ws = _workspace(query('dgmc_wgrad_workspace', k, m, n), g.device)
-                call('dgmc_wgrad', g, g.stride(0), RowStrided(x), x.stride(0), k, m, n, dw, db, ws,
-                     ws.numel(), stream_ptr())
-            else:
-                if grp.partial is None:
-                    grp.splits = query('dgmc_wgrad_splits', k, m, n)
-                    grp.partial = torch.empty(grp.calls * grp.splits, m * n, dtype=torch.float32,
-                                              device=g.device)
-                    grp.partial_b = torch.empty(grp.calls * grp.splits, m, dtype=torch.float32,
-                                                device=g.device) if ctx.has_bias else None
-                off = ctx.slot * grp.splits
-                call('dgmc_wgrad_partial', g, g.stride(0), RowStrided(x), x.stride(0), k, m, n,
-                     grp.partial[off:off + grp.splits],
-                     None if grp.partial_b is None else grp.partial_b[off:off + grp.splits], stream_ptr())
-                grp.done += 1
-                if grp.done == grp.calls:  # last backward of this weight: reduce everything once
-                    dw = torch.empty_like(weight)
-                    db = torch.empty(m, dtype=torch.float32, device=g.device) if ctx.has_bias else None
-                    call('dgmc_wgrad_reduce', grp.partial, grp.partial_b, grp.calls * grp.splits, m, n,
-                         dw, db, stream_ptr())
-                    grp.partial = grp.partial_b = None
-                    grp.done = 0  # a second backward over a retained graph starts afresh
+                call('dgmc_wgrad_reduce', holder.partial, holder.partial_b, calls * holder.splits, m, n,
+                     dw, db, stream_ptr())
+                holder.partial = holder.partial_b = None
+                holder.done = 0  # a second backward over a retained graph starts afresh
         return dx, dw, db, None, None
 
 

@@ -198,6 +198,15 @@ int dgmc_wgrad_reduce(const float* partial, const float* partial_b, int n_partia
 int dgmc_wgrad(const float* g, int64_t ldg, const float* x, int64_t ldx, int64_t k, int m, int n,
                float* dw, float* db, void* workspace, size_t workspace_bytes, dgmc_stream_t stream);
 
+/* Tensor-core variant of dgmc_wgrad_partial (same partial layout, same dgmc_wgrad_reduce): tcgen05
+ * kind::tf32 with every operand split into hi + lo and three MMAs per product (hi*hi + hi*lo + lo*hi,
+ * fp32 TMEM accumulator) — fp32-level accuracy (~2^-21 relative), used for the backward pass only.
+ * m <= 128 output channels (dgmc_wgrad_tc_supported). */
+int dgmc_wgrad_tc_supported(int m, int n);
+int dgmc_wgrad_tc_splits(int64_t k, int m, int n);
+int dgmc_wgrad_tc_partial(const float* g, int64_t ldg, const float* x, int64_t ldx, int64_t k, int m, int n,
+                          float* partial, float* partial_b, dgmc_stream_t stream);
+
 /* ---- dense branch: consensus update without materialising D [B, N_s, N_t, R] ----------------
  * s_out[b,i,j] = s_in[b,i,j] + [s_mask[b,i] & t_mask[b,j]] * (b2 + sum_c w2[c] relu(ps[b,i,c] - pt[b,j,c]))
  * replaces D = o_s[:, :, None] - o_t[:, None], mlp(D).masked_fill(~S_mask, 0) at dgmc.py:178-179

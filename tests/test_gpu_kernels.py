@@ -323,8 +323,10 @@ def test_balanced_kernels_with_hub_targets(r):
 
 @pytest.mark.parametrize('k,m,n', [(39000, 64, 192), (5000, 64, 256), (3000, 8, 24), (2500, 33, 70),
                                    (100000, 64, 64)])
-def test_node_linear_wgrad_matches_autograd(k, m, n):
+@pytest.mark.parametrize('tensor_core', [False, True])
+def test_node_linear_wgrad_matches_autograd(k, m, n, tensor_core, monkeypatch):
     from dgmc import ops
+    monkeypatch.setattr(ops, 'WGRAD_TENSOR_CORE', tensor_core)  # fp32 FFMA split-K / tcgen05 3xTF32
     g = _gen(k + m + n)
     x = _randn(g, k, n).requires_grad_()
     w = (_randn(g, m, n) * 0.1).requires_grad_()
