@@ -511,13 +511,20 @@ def main():
     stage('capturing e2e graph')
     e2e_step = GraphedTrainStep(model, opt, *args_of(d), structure_is_static=False)
     stage('e2e graph captured')
+    # Input pipelining: the host-to-device copy of step i+1 is issued (side stream, pinned memory)
+    # right after step i is launched and before its loss is read, so it overlaps step i's kernels;
+    # every step still copies its 49.5 MB from the host and reads its loss back.
     for _ in range(3):
-        e2e_step(*args_of(pinned)).item()
+        loss_t = e2e_step(*args_of(pinned))
+        e2e_step.prefetch(*args_of(pinned))
+        loss_t.item()
     barrier()
     start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     start.record()
     for _ in range(args.steps):
-        loss_value = e2e_step(*args_of(pinned)).item()
+        loss_t = e2e_step(*args_of(pinned))
+        e2e_step.prefetch(*args_of(pinned))
+        loss_value = loss_t.item()
     end.record()
     barrier()
     ms2 = torch.tensor([start.elapsed_time(end)], device=dev)

@@ -65,9 +65,43 @@ class GraphedTrainStep(object):
 
     def __call__(self, *inputs):
         """Copy the inputs into the captured buffers and replay.  Returns the (static) loss tensor;
-        reading it with .item() is the only host synchronisation."""
+        reading it with .item() is the only host synchronisation.  Inputs that were announced with
+        `prefetch()` are taken from the staging buffers (a device-to-device copy)."""
+        staged = self._staged_for(inputs)
+        if staged is not None:
+            torch.cuda.current_stream().wait_event(self._staged_event)
+            inputs = staged
         for dst, src in zip(self.static, inputs):
             if dst is not None and src is not dst:
                 dst.copy_(src, non_blocking=True)
+        if staged is not None:
+            self._consumed_event.record()   # staging buffers are free again from here on
         self.graph.replay()
         return self.loss
+
+    # ---- optional input pipelining ----------------------------------------------------------------
+    def prefetch(self, *inputs):
+        """Start copying the NEXT step's (pinned host) inputs to the device on a side stream while
+        the current step is still running; the following __call__ with the same tensors then only
+        pays a device-to-device copy.  Call it right after __call__ and before reading the loss."""
+        if not hasattr(self, '_copy_stream'):
+            self._copy_stream = torch.cuda.Stream()
+            self._staging = [None if t is None else torch.empty_like(t) for t in self.static]
+            self._staged_event = torch.cuda.Event()
+            self._consumed_event = torch.cuda.Event()
+            self._consumed_event.record()
+        # the staging buffers may still feed the previous __call__'s device-to-device copies; do NOT
+        # wait for the replay that follows them — overlapping it is the point
+        self._copy_stream.wait_event(self._consumed_event)
+        with torch.cuda.stream(self._copy_stream):
+            for dst, src in zip(self._staging, inputs):
+                if dst is not None:
+                    dst.copy_(src, non_blocking=True)
+            self._staged_event.record()
+        self._staged_ids = tuple(id(t) for t in inputs)
+
+    def _staged_for(self, inputs):
+        if getattr(self, '_staged_ids', None) == tuple(id(t) for t in inputs):
+            self._staged_ids = None
+            return self._staging
+        return None

@@ -47,3 +47,29 @@ def test_graphed_step_trains_and_reads_new_inputs(static_structure):
             _, S_L = model(*[None if t is None else t.cuda() for t in other][:-1])
             eager = model.loss(S_L, other[-1].cuda()).item()
         assert abs(eager - b) < 0.5 * max(abs(b), 0.1) + 0.5
+
+
+def test_prefetch_pipelines_inputs_without_changing_results():
+    from dgmc.models import DGMC, RelCNN
+    from dgmc.utils import GraphedTrainStep
+    torch.manual_seed(0)
+    model = DGMC(RelCNN(24, 32, 2, dropout=0.0), RelCNN(8, 8, 2), num_steps=2, k=5).cuda().eval()
+    # eval-mode model + zero learning rate: the step's loss depends on the inputs only (up to the
+    # random indicators), so feeding pair A / pair B alternately must give alternating losses
+    opt = torch.optim.Adam(model.parameters(), lr=0.0, capturable=True)
+    a = [None if t is None else t.pin_memory() for t in _problem(1)]
+    b = [None if t is None else t.pin_memory() for t in _problem(2)]
+    step = GraphedTrainStep(model, opt, *[None if t is None else t.cuda() for t in a],
+                            structure_is_static=False)
+    plain = [step(*(a if i % 2 == 0 else b)).item() for i in range(6)]
+    piped = []
+    loss = step(*a)
+    for i in range(6):
+        nxt = b if i % 2 == 0 else a
+        step.prefetch(*nxt)
+        piped.append(loss.item())
+        loss = step(*nxt)
+    mean = lambda v: sum(v) / len(v)  # noqa: E731
+    assert abs(mean(plain[0::2]) - mean(piped[0::2])) < 0.05 * abs(mean(plain[0::2])) + 1e-3
+    assert abs(mean(plain[1::2]) - mean(piped[1::2])) < 0.05 * abs(mean(plain[1::2])) + 1e-3
+    assert abs(mean(plain[0::2]) - mean(plain[1::2])) > 1e-3   # the two pairs really differ
