@@ -34,9 +34,9 @@ struct BalArgs {
 };
 
 template <int G, int NV, int MODE>
-__global__ void __launch_bounds__(256) balanced_main_kernel(const BalArgs a) {
+__global__ void __launch_bounds__(256, NV == 1 ? 4 : 1) balanced_main_kernel(const BalArgs a) {
     constexpr int PER = CB / G;  // metadata entries held per lane
-    constexpr int BR = NV <= 2 ? 8 : 4;  // source rows in flight per lane group
+    constexpr int BR = NV == 2 ? 8 : 4;  // source rows in flight per lane group
     const int lane = threadIdx.x & 31, gl = lane % G;
     const unsigned gmask = G == 32 ? 0xffffffffu : (((1u << G) - 1u) << (lane - gl));
     const long long groups = (long long)gridDim.x * (blockDim.x / G);
