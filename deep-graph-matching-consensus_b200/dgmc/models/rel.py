@@ -30,7 +30,8 @@ class RelConv(torch.nn.Module):
         fused into the GEMM epilogue."""
         graph = ops.GraphCSR.of(edge_index, x.size(0))
         stacked = ops.rel_aggregate(x, graph)  # [N, 3 C_in] = [x | mean_in | mean_out]
-        weight = torch.cat([self.root.weight, self.lin1.weight, self.lin2.weight], dim=1)
+        weight = ops.region_cached(('relconv', id(self)), lambda: torch.cat(
+            [self.root.weight, self.lin1.weight, self.lin2.weight], dim=1))
         return ops.node_linear(stacked, weight, self.root.bias, relu=relu, key=('relconv', id(self)))
 
     def __repr__(self):

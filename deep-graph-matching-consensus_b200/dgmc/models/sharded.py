@@ -154,7 +154,8 @@ def sharded_relcnn(psi, x_gathered, sp, group):
     full = x_gathered
     for i, conv in enumerate(psi.convs):
         stacked = ops.rel_aggregate_op(full, sp.rel)                      # [n_loc, 3 C]
-        weight = torch.cat([conv.root.weight, conv.lin1.weight, conv.lin2.weight], dim=1)
+        weight = ops.region_cached(('relconv', id(conv)), lambda c=conv: torch.cat(
+            [c.root.weight, c.lin1.weight, c.lin2.weight], dim=1))
         h = ops.node_linear(stacked, weight, conv.root.bias, relu=True, key=('relconv', id(conv)))
         feats.append(h)
         if i + 1 < len(psi.convs):

@@ -378,6 +378,18 @@ class deferred_wgrad(object):
         _DEFER[0] = self.prev
 
 
+def region_cached(key, make):
+    """Value shared by all uses inside the current deferred_wgrad() region (e.g. the concatenated
+    RelConv weight, identical for every consensus step); computed on the spot outside a region."""
+    region = _DEFER[0]
+    if region is None or not torch.is_grad_enabled():
+        return make()
+    slot = ('cache', ) + tuple(key)
+    if slot not in region:
+        region[slot] = make()
+    return region[slot]
+
+
 class _NodeLinear(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, bias, relu, group):
