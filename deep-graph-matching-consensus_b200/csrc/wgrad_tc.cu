@@ -26,7 +26,6 @@ constexpr int WT_THREADS = 128;
 constexpr int WT_A_BYTES = WT_TN * WT_KC * 4;   // 16 KB
 constexpr int WT_MAX_M = 128;                   // output channels (UMMA N), padded to 64 or 128
 constexpr int WT_B_BYTES = WT_MAX_M * WT_KC * 4;  // 16 KB
-constexpr int WT_STAGE_BYTES = 2 * WT_A_BYTES + 2 * WT_B_BYTES;  // hi + lo of both operands
 
 // byte offset of element (row, k) in a K-major [rows x 32 fp32] tile with 128-byte swizzle
 __device__ __forceinline__ uint32_t sw128_offset(int row, int k) {
@@ -38,13 +37,15 @@ __device__ __forceinline__ void split_tf32(float v, float& hi, float& lo) {
     lo = v - hi;
 }
 
-__global__ void __launch_bounds__(WT_THREADS, 1)
+__global__ void __launch_bounds__(WT_THREADS, 2)
 wgrad_tc_kernel(const float* __restrict__ g, long long ldg_, const float* __restrict__ x, long long ldx,
                 long long K, int M, int N, int m_pad, int splits, float* __restrict__ partial,
                 float* __restrict__ partial_b) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 2 * WT_STAGE_BYTES);
+    const int b_bytes = m_pad * WT_KC * 4;                       // 8 KB (m_pad = 64) or 16 KB
+    const int stage_bytes = 2 * WT_A_BYTES + 2 * b_bytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 2 * stage_bytes);
     uint64_t* stage_free = bars;      // [2]  arrives via tcgen05.commit
     uint64_t* all_done = bars + 2;    // [1]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3);
@@ -86,44 +87,59 @@ wgrad_tc_kernel(const float* __restrict__ g, long long ldg_, const float* __rest
     const bool a_live = n0 + tid < N, b_live = b_row < M;
     float bsum = 0.f;                                       // column sum of G for channel b_row
     const int n_chunks = (int)((k_end - k_begin + WT_KC - 1) / WT_KC);
+    float na[WT_KC], nb[WT_KC];       // next chunk: 32 k of this thread's X channel, up to 32 k of its G channel
+    auto fetch = [&](long long k0) {
+#pragma unroll
+        for (int kk = 0; kk < WT_KC; ++kk)
+            na[kk] = (a_live && k0 + kk < k_end) ? __ldg(x + (k0 + kk) * ldx + n0 + tid) : 0.f;
+#pragma unroll
+        for (int j = 0; j < WT_KC / 4; ++j) {                 // m_pad = 64: only j < 4 is in range
+            const int kq = b_k0 + j * b_kstep;
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                nb[4 * j + u] = (b_live && kq < WT_KC && k0 + kq + u < k_end)
+                                    ? __ldg(g + (k0 + kq + u) * ldg_ + b_row) : 0.f;
+        }
+    };
+    if (n_chunks > 0) fetch(k_begin);
     for (int c = 0; c < (n_chunks > 0 ? n_chunks : 0); ++c) {
         const int stage = c & 1;
-        uint8_t* a_hi = smem + stage * WT_STAGE_BYTES;
+        uint8_t* a_hi = smem + stage * stage_bytes;
         uint8_t* a_lo = a_hi + WT_A_BYTES;
         uint8_t* b_hi = a_lo + WT_A_BYTES;
-        uint8_t* b_lo = b_hi + WT_B_BYTES;
+        uint8_t* b_lo = b_hi + b_bytes;
         if (c >= 2) mbar_wait(&stage_free[stage], (uint32_t)(((c >> 1) - 1) & 1));  // MMAs of chunk c-2 retired
-        const long long k0 = k_begin + (long long)c * WT_KC;
+        // the values of this chunk were fetched one iteration ago; fetch the next chunk now so that
+        // its global-memory latency hides behind this chunk's split / st.shared / MMA issue
+        float va[WT_KC], vb[WT_KC];
+#pragma unroll
+        for (int i = 0; i < WT_KC; ++i) va[i] = na[i];
+#pragma unroll
+        for (int i = 0; i < WT_KC; ++i) vb[i] = nb[i];
+        if (c + 1 < n_chunks) fetch(k_begin + (long long)(c + 1) * WT_KC);
         // ---- X chunk [32 x 128] -> A tiles (row = input channel, column = k) ----
-        {
-            float v[WT_KC];
 #pragma unroll
-            for (int kk = 0; kk < WT_KC; ++kk)
-                v[kk] = (a_live && k0 + kk < k_end) ? __ldg(x + (k0 + kk) * ldx + n0 + tid) : 0.f;
-#pragma unroll
-            for (int kq = 0; kq < WT_KC; kq += 4) {
-                float4 hi, lo;
-                split_tf32(v[kq], hi.x, lo.x); split_tf32(v[kq + 1], hi.y, lo.y);
-                split_tf32(v[kq + 2], hi.z, lo.z); split_tf32(v[kq + 3], hi.w, lo.w);
-                const uint32_t o = sw128_offset(tid, kq);
-                *reinterpret_cast<float4*>(a_hi + o) = hi;
-                *reinterpret_cast<float4*>(a_lo + o) = lo;
-            }
+        for (int kq = 0; kq < WT_KC; kq += 4) {
+            float4 hi, lo;
+            split_tf32(va[kq], hi.x, lo.x); split_tf32(va[kq + 1], hi.y, lo.y);
+            split_tf32(va[kq + 2], hi.z, lo.z); split_tf32(va[kq + 3], hi.w, lo.w);
+            const uint32_t o = sw128_offset(tid, kq);
+            *reinterpret_cast<float4*>(a_hi + o) = hi;
+            *reinterpret_cast<float4*>(a_lo + o) = lo;
         }
         // ---- G chunk [32 x m_pad] -> B tiles (row = output channel, column = k) ----
-        for (int kq = b_k0; kq < WT_KC; kq += b_kstep) {
-            float v[4];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                v[u] = (b_live && k0 + kq + u < k_end) ? __ldg(g + (k0 + kq + u) * ldg_ + b_row) : 0.f;
-                bsum += v[u];
+        for (int j = 0; j < WT_KC / 4; ++j) {                 // k-quadruples of this thread (m_pad = 64: 4 in range)
+            const int kq = b_k0 + j * b_kstep;
+            if (kq < WT_KC) {
+                float4 hi, lo;
+                split_tf32(vb[4 * j], hi.x, lo.x); split_tf32(vb[4 * j + 1], hi.y, lo.y);
+                split_tf32(vb[4 * j + 2], hi.z, lo.z); split_tf32(vb[4 * j + 3], hi.w, lo.w);
+                bsum += (vb[4 * j] + vb[4 * j + 1]) + (vb[4 * j + 2] + vb[4 * j + 3]);
+                const uint32_t o = sw128_offset(b_row, kq);
+                *reinterpret_cast<float4*>(b_hi + o) = hi;
+                *reinterpret_cast<float4*>(b_lo + o) = lo;
             }
-            float4 hi, lo;
-            split_tf32(v[0], hi.x, lo.x); split_tf32(v[1], hi.y, lo.y);
-            split_tf32(v[2], hi.z, lo.z); split_tf32(v[3], hi.w, lo.w);
-            const uint32_t o = sw128_offset(b_row, kq);
-            *reinterpret_cast<float4*>(b_hi + o) = hi;
-            *reinterpret_cast<float4*>(b_lo + o) = lo;
         }
         fence_proxy_async_smem();     // st.shared above -> UMMA operand reads below
         __syncthreads();
@@ -179,7 +195,7 @@ wgrad_tc_kernel(const float* __restrict__ g, long long ldg_, const float* __rest
     }
 }
 
-constexpr size_t WT_SMEM = 2 * WT_STAGE_BYTES + 64 + 8 * 128 * 4 + 1024;
+static size_t wt_smem(int m_pad) { return 2 * (size_t)(2 * WT_A_BYTES + 2 * m_pad * WT_KC * 4) + 64 + 128 * 4 + 1024; }
 
 }  // namespace tc
 }  // namespace dgmc
@@ -188,7 +204,7 @@ using namespace dgmc;
 
 static int wgrad_tc_splits_impl(long long K, int N) {
     const int tiles = (N + tc::WT_TN - 1) / tc::WT_TN;
-    int splits = (2 * sm_count() + tiles - 1) / tiles;
+    int splits = (2 * sm_count() + tiles - 1) / tiles;     // one wave at 2 CTAs per SM
     const long long max_by_k = (K + 8 * tc::WT_KC - 1) / (8 * tc::WT_KC);   // >= 256 rows per split
     if (splits > max_by_k) splits = (int)max_by_k;
     if (splits < 1) splits = 1;
@@ -210,19 +226,20 @@ extern "C" int dgmc_wgrad_tc_partial(const float* g, int64_t ldg, const float* x
         set_error("wgrad_tc_partial: m=%d unsupported (1..%d output channels)", m, tc::WT_MAX_M);
         return DGMC_ERR_UNSUPPORTED;
     }
-    static bool configured = false;
-    if (!configured) {
+    const int m_pad = m <= 64 ? 64 : 128;
+    const size_t smem = tc::wt_smem(m_pad);
+    static size_t configured = 0;
+    if (smem > configured) {
         if (cudaFuncSetAttribute(tc::wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)tc::WT_SMEM) != cudaSuccess) {
-            set_error("wgrad_tc_partial: cannot set %zu bytes of dynamic shared memory", tc::WT_SMEM);
+                                 (int)smem) != cudaSuccess) {
+            set_error("wgrad_tc_partial: cannot set %zu bytes of dynamic shared memory", smem);
             return DGMC_ERR_CUDA;
         }
-        configured = true;
+        configured = smem;
     }
     const int splits = wgrad_tc_splits_impl(k, n);
-    const int m_pad = m <= 64 ? 64 : 128;
     dim3 grid((n + tc::WT_TN - 1) / tc::WT_TN, splits);
-    tc::wgrad_tc_kernel<<<grid, tc::WT_THREADS, tc::WT_SMEM, stream>>>(g, ldg, x, ldx, k, m, n, m_pad, splits,
+    tc::wgrad_tc_kernel<<<grid, tc::WT_THREADS, smem, stream>>>(g, ldg, x, ldx, k, m, n, m_pad, splits,
                                                                       partial, partial_b);
     return check_launch("wgrad_tc_partial");
 }
