@@ -245,6 +245,7 @@ static int check_r(const char* who, int r) {
 extern "C" int dgmc_diff_mlp_fwd(const float* s_in, const float* ps, const float* pt,
                                  const int32_t* idx, const float* w2, const float* b2, float* s_out,
                                  int64_t m, int k, int r, dgmc_stream_t stream) {
+    if (m == 0 && k >= 1) return DGMC_OK;
     DGMC_REQUIRE(s_in && ps && pt && idx && w2 && b2 && s_out && m >= 0 && k >= 1,
                  "diff_mlp_fwd: bad arguments");
     if (int e = check_r("diff_mlp_fwd", r)) return e;

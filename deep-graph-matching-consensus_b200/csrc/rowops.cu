@@ -187,6 +187,7 @@ using namespace dgmc;
 
 extern "C" int dgmc_softmax_k_fwd(const float* x, float* y, int64_t rows, int k,
                                   dgmc_stream_t stream) {
+    if (rows == 0 && k >= 1) return DGMC_OK;   // empty input: pointers may be null
     DGMC_REQUIRE(x && y && rows >= 0 && k >= 1, "softmax_k_fwd: bad arguments (rows=%lld k=%d)",
                  (long long)rows, k);
     if (rows == 0) return DGMC_OK;
@@ -199,6 +200,7 @@ extern "C" int dgmc_softmax_k_fwd(const float* x, float* y, int64_t rows, int k,
 
 extern "C" int dgmc_softmax_k_bwd(const float* y, const float* dy, float* dx, int64_t rows, int k,
                                   dgmc_stream_t stream) {
+    if (rows == 0 && k >= 1) return DGMC_OK;
     DGMC_REQUIRE(y && dy && dx && rows >= 0 && k >= 1, "softmax_k_bwd: bad arguments");
     if (rows == 0) return DGMC_OK;
     return launch_by_group(k, [&](auto G) {
@@ -231,6 +233,7 @@ extern "C" int dgmc_masked_softmax_bwd(const float* y, const float* dy, float* d
 extern "C" int dgmc_gather_dot_fwd(const float* a, int64_t lda, const float* b, int64_t ldb,
                                    const int32_t* idx, float* out, int64_t m, int k, int c,
                                    dgmc_stream_t stream) {
+    if (m == 0 && k >= 1 && c >= 1) return DGMC_OK;
     DGMC_REQUIRE(a && b && idx && out && m >= 0 && k >= 1 && c >= 1 && lda >= c && ldb >= c,
                  "gather_dot_fwd: bad arguments (m=%lld k=%d c=%d)", (long long)m, k, c);
     if (m == 0) return DGMC_OK;
