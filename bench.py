@@ -368,6 +368,7 @@ def main():
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--cpu-budget', type=float, default=None, help='seconds of CPU baseline work')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--k', type=int, default=0, help='override the sparsity k (BASELINE.json configs[3] uses 25)')
     ap.add_argument('--nodes', type=int, default=0, metavar='N',
                     help='scaling study: replace the DBP15K shape by an N x N-node pair (5 edges per '
                          'node, N/4 train pairs); not the headline configuration')
@@ -384,6 +385,8 @@ def main():
     world = int(os.environ.get('WORLD_SIZE', 1))
     local = int(os.environ.get('LOCAL_RANK', 0))
     w = dict(WORKLOAD)
+    if args.k:
+        w['k'] = args.k
     if args.nodes:
         w.update(name='synthetic %d x %d-node pair (scaling study)' % (args.nodes, args.nodes),
                  n_s=args.nodes, n_t=args.nodes, e_s=5 * args.nodes, e_t=5 * args.nodes,
@@ -575,7 +578,7 @@ def main():
             'eager_ms_per_step': eager_ms,
             'roofline': roofline, 'roofline_all': rl,
         }
-        if world == 1 and not args.no_cpu_baseline and not args.nodes:
+        if world == 1 and not args.no_cpu_baseline and not args.nodes and not args.k:
             sps, n, cores, dt, _ = cpu_reference_steps(w, host, 2, 1, args.cpu_budget or 30.0)
             out['cpu_baseline'] = {
                 'value': sps, 'unit': 'steps/s', 'cores': cores, 'kind': 'port',
