@@ -243,7 +243,10 @@ def kernel_rooflines(w, model, e_t, peaks, step_ms, iters=5):
     hbm, tf = peaks['hbm_gbs'], peaks['bf16_tflops']
     rows = []
 
+    logical = {}
+
     def pick(table_bytes, b_min, b_logical):
+        logical['last'] = b_logical
         return (b_logical, 'logical') if table_bytes > l2 else (b_min, 'min')
 
     dbp15k = (n_s, n_t, C, R) == (19388, 19572, 256, 64)
@@ -256,6 +259,7 @@ def kernel_rooflines(w, model, e_t, peaks, step_ms, iters=5):
         rows.append({'kernel': name, 'bound': bound, 'achieved': round(achieved, 2), 'peak': peak,
                      'unit': 'TFLOP/s' if bound == 'tensor' else 'GB/s',
                      'frac': round(achieved / peak, 4), 'traffic': traffic, 'work_basis': basis,
+                     'logical_gbs': round(logical.pop('last') / (ms * 1e-3) / 1e9, 1) if 'last' in logical else None,
                      'ms_per_launch': round(ms, 4), 'launches_per_step': calls,
                      'share_of_step': round(ms * calls / step_ms, 4) if step_ms else None})
 
