@@ -88,3 +88,14 @@ def test_cpu_tensors_fail_loudly():
     e = torch.tensor([[0, 1, 2], [1, 2, 3]])
     with pytest.raises(native.DgmcNativeError):
         model(x, e, None, None, x, e, None, None)
+
+
+def test_training_step_is_bit_reproducible():
+    """No atomics anywhere on the path (every scatter is a segmented gather over a stably sorted CSR,
+    reductions are two-stage in a fixed order): two runs of the same step agree bit for bit."""
+    case = load_case('sparse_rel_train')
+    a, b = run_product(case), run_product(case)
+    assert torch.equal(a['S_L'], b['S_L']) and torch.equal(a['idx'], b['idx'])
+    assert torch.equal(a['loss_L'], b['loss_L'])
+    for name, grad in a['grads'].items():
+        assert torch.equal(grad, b['grads'][name]), name
