@@ -329,6 +329,17 @@ def pascal_step_bench(dev, steps, warmup):
     b.record()
     torch.cuda.synchronize()
     ms = a.elapsed_time(b) / steps
+    if os.environ.get('DGMC_BENCH_KINETO'):
+        from torch.profiler import ProfilerActivity, profile
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            for _ in range(3):
+                step()
+            torch.cuda.synchronize()
+        rows = sorted(((e.key, e.count, e.device_time_total) for e in prof.key_averages()
+                       if e.device_time_total > 0), key=lambda r: -r[2])
+        print('kernel time per step: %.3f ms' % (sum(r[2] for r in rows) / 3e3), file=sys.stderr)
+        for name, cnt, t in rows[:25]:
+            print('%8.1f us/step %5d x  %s' % (t / 3, cnt // 3, name[:110]), file=sys.stderr)
     emit({'pascal_shaped': {'graph_pairs': B, 'nodes': int(x_s.size(0)), 'edges': int(e_s.size(1)),
                             'ms_per_step': ms, 'steps_per_s': 1e3 / ms, 'pairs_per_s': B * 1e3 / ms,
                             'loss': loss.item(), 'execution': 'eager (batch sizes vary per step in '

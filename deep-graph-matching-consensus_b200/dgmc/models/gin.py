@@ -1,6 +1,6 @@
 """GIN backbone (reference: dgmc/models/gin.py:9-59; PyG GINConv is third-party).  Used by the
 reference's tests as psi_1/psi_2 (test/models/test_dgmc.py:9-10).  The neighbour sum runs on the
-K5 segmented-gather kernel; the MLPs are library GEMMs."""
+K5 segmented-gather kernel; the MLPs on the per-node GEMM (ops.node_linear)."""
 import torch
 
 from .mlp import MLP
@@ -55,7 +55,7 @@ class GIN(torch.nn.Module):
         for conv in self.convs:
             feats.append(conv(feats[-1], edge_index))
         out = torch.cat(feats, dim=-1) if self.cat else feats[-1]
-        return self.final(out) if self.lin else out
+        return ops.node_linear(out, self.final.weight, self.final.bias) if self.lin else out
 
     def __repr__(self):
         return '{}({}, {}, num_layers={}, batch_norm={}, cat={}, lin={})'.format(

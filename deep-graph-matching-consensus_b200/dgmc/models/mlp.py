@@ -1,8 +1,10 @@
 """MLP backbone (reference: dgmc/models/mlp.py:7-44).  Only ever used inside GIN, which only the
-reference's unit tests use; SURVEY.md §2 marks it out of scope for kernels, so it is a plain
-PyTorch host module kept for API completeness (same constructor, state_dict names and repr)."""
+reference's unit tests use (same constructor, state_dict names and repr).  Its Linear layers run on
+the shared per-node GEMM (ops.node_linear: tensor-core kernel on CUDA)."""
 import torch
 import torch.nn.functional as F
+
+from .. import ops
 
 
 class MLP(torch.nn.Module):
@@ -26,9 +28,8 @@ class MLP(torch.nn.Module):
         for i in range(self.num_layers):
             if i == last:
                 x = F.dropout(x, p=self.dropout, training=self.training)
-            x = self.lins[i](x)
+            x = ops.node_linear(x, self.lins[i].weight, self.lins[i].bias, relu=(i != last))
             if i != last:
-                x = F.relu(x)
                 if self.batch_norm:
                     x = self.batch_norms[i](x)
         return x

@@ -4,7 +4,7 @@ torch_spline_conv are third-party) on the K5 spline kernels.
 SplineConv(in, out, dim, kernel_size=5): degree-1 open B-spline kernel, mean aggregation, root
 weight and bias.  Parameters: `weight [K^dim, in, out]`, `root [in, out]`, `bias [out]`
 (PyG changed these names between releases; copy weights explicitly when converting checkpoints).
-The B200 path transforms first — Y = x @ W for all K^dim kernels in one library GEMM — and then
+The B200 path transforms first — Y = x @ W for all K^dim kernels in one GEMM (ops.node_linear) — and then
 runs a deterministic CSR gather over the in-edges weighted by the cached B-spline basis."""
 import math
 
@@ -39,8 +39,8 @@ class SplineConv(torch.nn.Module):
         if pad:
             weight, root, bias = F.pad(weight, (0, pad)), F.pad(root, (0, pad)), F.pad(bias, (0, pad))
         wide = weight.permute(1, 0, 2).reshape(self.in_channels, self.n_kernels * (c + pad))
-        y = x @ wide  # [N, K * C]
-        base = torch.addmm(bias, x, root)
+        y = ops.node_linear(x, wide, kn=True)  # [N, K * C]
+        base = ops.node_linear(x, root, bias, kn=True)
         out = ops.spline_gather(y, base, graph, sb, self.n_kernels)
         return out[:, :c] if pad else out
 
@@ -79,7 +79,7 @@ class SplineCNN(torch.nn.Module):
             feats.append(F.relu(conv(feats[-1], edge_index, edge_attr)))
         out = torch.cat(feats, dim=-1) if self.cat else feats[-1]
         out = F.dropout(out, p=self.dropout, training=self.training)
-        return self.final(out) if self.lin else out
+        return ops.node_linear(out, self.final.weight, self.final.bias) if self.lin else out
 
     def __repr__(self):
         return ('{}({}, {}, dim={}, num_layers={}, cat={}, lin={}, dropout={})').format(

@@ -362,6 +362,7 @@ class WGradGroup(object):
         self.done = 0           # backward passes seen
         self.partial = self.partial_b = None
         self.splits = 0
+        self.split_fwd = self.split_bwd = None   # hi / lo copies of the weight for dgmc_linear_tc
 
 
 _DEFER = [None]  # {key: WGradGroup} while a deferred-wgrad region is active
@@ -390,16 +391,56 @@ def region_cached(key, make):
     return region[slot]
 
 
+LINEAR_TENSOR_CORE = False  # forward / input-gradient GEMMs on dgmc_linear_tc (tcgen05, 3xTF32); off until validated end to end
+
+
+def _linear_tc_ok(x, n_out, k_in):
+    return LINEAR_TENSOR_CORE and x.is_cuda and x.dtype == torch.float32 and x.dim() == 2 \
+        and x.stride(1) == 1 and x.size(0) >= 1 \
+        and bool(query('dgmc_linear_tc_supported', x.size(0), n_out, k_in, x.stride(0), x.data_ptr()))
+
+
+def _split_weight(weight, transposed, holder=None, slot=None):
+    """hi / lo split (K-major, padded) of a weight for dgmc_linear_tc; `transposed`: weight is
+    [k_in, n_out].  Cached on `holder` (a WGradGroup: one forward pass of one weight)."""
+    if holder is not None and getattr(holder, slot) is not None:
+        return getattr(holder, slot)
+    weight = weight.contiguous()
+    k_in, n_out = (weight.size(0), weight.size(1)) if transposed else (weight.size(1), weight.size(0))
+    ws = torch.empty(query('dgmc_linear_tc_workspace', n_out, k_in), dtype=torch.uint8,
+                     device=weight.device)
+    call('dgmc_linear_tc_split_weight', weight, weight.stride(0), int(transposed), n_out, k_in, ws,
+         ws.numel(), stream_ptr())
+    if holder is not None:
+        setattr(holder, slot, ws)
+    return ws
+
+
+def _linear_tc(x, split, bias, relu, n_out, k_in):
+    y = torch.empty(x.size(0), n_out, dtype=torch.float32, device=x.device)
+    call('dgmc_linear_tc', RowStrided(x), x.stride(0), split, bias, int(relu), y, n_out, x.size(0),
+         n_out, k_in, stream_ptr())
+    return y
+
+
 class _NodeLinear(torch.autograd.Function):
+    """kn = False: weight [out, in] (torch Linear); kn = True: weight [in, out] (SplineConv)."""
     @staticmethod
-    def forward(ctx, x, weight, bias, relu, group):
-        if relu:  # bias + ReLU in the library GEMM's epilogue
-            y = torch._addmm_activation(bias, x, weight.t(), use_gelu=False)
+    def forward(ctx, x, weight, bias, relu, group, kn):
+        k_in, n_out = (weight.size(0), weight.size(1)) if kn else (weight.size(1), weight.size(0))
+        if _linear_tc_ok(x, n_out, k_in):
+            y = _linear_tc(x, _split_weight(weight, kn, group, 'split_fwd'), bias, relu, n_out, k_in)
+        else:
+            w_kn = weight if kn else weight.t()
+            if relu:  # bias + ReLU in the library GEMM's epilogue
+                y = torch._addmm_activation(bias, x, w_kn, use_gelu=False)
+            else:
+                y = torch.addmm(bias, x, w_kn) if bias is not None else x @ w_kn
+        if relu:
             ctx.save_for_backward(x, weight, y)
         else:
-            y = torch.addmm(bias, x, weight.t()) if bias is not None else x @ weight.t()
             ctx.save_for_backward(x, weight)
-        ctx.has_bias, ctx.relu, ctx.group = bias is not None, relu, group
+        ctx.has_bias, ctx.relu, ctx.group, ctx.kn = bias is not None, relu, group, kn
         if group is not None:
             ctx.slot = group.calls
             group.calls += 1
@@ -413,52 +454,76 @@ class _NodeLinear(torch.autograd.Function):
         else:
             x, weight = ctx.saved_tensors
         g = _f32(g)
-        k, m, n = x.size(0), weight.size(0), weight.size(1)
-        dx = g @ weight if ctx.needs_input_grad[0] else None
+        kn = ctx.kn
+        k_in, n_out = (weight.size(0), weight.size(1)) if kn else (weight.size(1), weight.size(0))
+        k = x.size(0)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            if g.stride(1) != 1:
+                g = g.contiguous()
+            if _linear_tc_ok(g, k_in, n_out):  # dx = g W: the same kernel on the transposed weight
+                dx = _linear_tc(g, _split_weight(weight, not kn, ctx.group, 'split_bwd'), None, False,
+                                k_in, n_out)
+            else:
+                dx = g @ (weight.t() if kn else weight)
         dw = db = None
-        if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
-            grp = ctx.group
-            # fp32 FFMA split-K kernel by default; WGRAD_TENSOR_CORE switches to the tcgen05 3xTF32
-            # kernel (correct, but staging-bound and 2x slower at these skinny shapes: DESIGN.md §8)
-            tc = WGRAD_TENSOR_CORE and bool(query('dgmc_wgrad_tc_supported', m, n))
-            fn_splits = 'dgmc_wgrad_tc_splits' if tc else 'dgmc_wgrad_splits'
-            fn_partial = 'dgmc_wgrad_tc_partial' if tc else 'dgmc_wgrad_partial'
-            calls, slot = (1, 0) if grp is None else (grp.calls, ctx.slot)
-            holder = grp if grp is not None else WGradGroup()
-            if holder.partial is None:
-                holder.splits = query(fn_splits, k, m, n)
-                holder.partial = torch.empty(calls * holder.splits, m * n, dtype=torch.float32,
-                                             device=g.device)
-                holder.partial_b = torch.empty(calls * holder.splits, m, dtype=torch.float32,
-                                               device=g.device) if ctx.has_bias else None
-            off = slot * holder.splits
-            call(fn_partial, g, g.stride(0), RowStrided(x), x.stride(0), k, m, n,
-                 holder.partial[off:off + holder.splits],
-                 None if holder.partial_b is None else holder.partial_b[off:off + holder.splits],
-                 stream_ptr())
-            holder.done += 1
-            if holder.done == calls:  # last backward of this weight: reduce everything once
-                dw = torch.empty_like(weight)
-                db = torch.empty(m, dtype=torch.float32, device=g.device) if ctx.has_bias else None
-                call('dgmc_wgrad_reduce', holder.partial, holder.partial_b, calls * holder.splits, m, n,
-                     dw, db, stream_ptr())
-                holder.partial = holder.partial_b = None
-                holder.done = 0  # a second backward over a retained graph starts afresh
-        return dx, dw, db, None, None
+        want_w = ctx.needs_input_grad[1]
+        want_b = ctx.has_bias and ctx.needs_input_grad[2]
+        if not (want_w or want_b):
+            return dx, None, None, None, None, None
+        if kn or weight.numel() > 64 * 1024 or k < 2048:
+            # large output or few rows: an ordinary GEMM, left to the library
+            if want_w:
+                dw = x.t() @ g if kn else g.t() @ x
+            if want_b:
+                db = g.sum(0)
+            return dx, dw, db, None, None, None
+        m, n = n_out, k_in
+        grp = ctx.group
+        # fp32 FFMA split-K kernel by default; WGRAD_TENSOR_CORE switches to the tcgen05 3xTF32
+        # kernel (correct, but staging-bound and 2x slower at these skinny shapes: DESIGN.md §8)
+        tc = WGRAD_TENSOR_CORE and bool(query('dgmc_wgrad_tc_supported', m, n))
+        fn_splits = 'dgmc_wgrad_tc_splits' if tc else 'dgmc_wgrad_splits'
+        fn_partial = 'dgmc_wgrad_tc_partial' if tc else 'dgmc_wgrad_partial'
+        calls, slot = (1, 0) if grp is None else (grp.calls, ctx.slot)
+        holder = grp if grp is not None else WGradGroup()
+        if holder.partial is None:
+            holder.splits = query(fn_splits, k, m, n)
+            holder.partial = torch.empty(calls * holder.splits, m * n, dtype=torch.float32,
+                                         device=g.device)
+            holder.partial_b = torch.empty(calls * holder.splits, m, dtype=torch.float32,
+                                           device=g.device) if ctx.has_bias else None
+        off = slot * holder.splits
+        call(fn_partial, g, g.stride(0), RowStrided(x), x.stride(0), k, m, n,
+             holder.partial[off:off + holder.splits],
+             None if holder.partial_b is None else holder.partial_b[off:off + holder.splits],
+             stream_ptr())
+        holder.done += 1
+        if holder.done == calls:  # last backward of this weight: reduce everything once
+            dw = torch.empty_like(weight)
+            db = torch.empty(m, dtype=torch.float32, device=g.device) if ctx.has_bias else None
+            call('dgmc_wgrad_reduce', holder.partial, holder.partial_b, calls * holder.splits, m, n,
+                 dw, db, stream_ptr())
+            holder.partial = holder.partial_b = None
+            holder.split_fwd = holder.split_bwd = None
+            holder.done = 0  # a second backward over a retained graph starts afresh
+        return dx, dw, db, None, None, None
 
 
-def node_linear(x, weight, bias=None, relu=False, key=None):
-    """relu?(x [nodes, in] @ weight[out, in]^T + bias): library GEMM forward (bias and ReLU in its
-    epilogue) and input gradient; the weight / bias gradient (a reduction over all nodes with a tiny
-    output) runs on the split-K kernel dgmc_wgrad when the output is small, else stays with the
-    library."""
-    if weight.size(0) * weight.size(1) <= 64 * 1024 and x.size(0) >= 2048 and x.is_cuda \
-            and x.dtype == torch.float32 and x.stride(1) == 1 and (bias is not None or not relu):
+def node_linear(x, weight, bias=None, relu=False, key=None, kn=False):
+    """relu?(x [nodes, in] @ W + bias) with W = weight[out, in]^T (kn=False) or weight[in, out]
+    (kn=True).  Forward and input gradient run on the tensor-core kernel dgmc_linear_tc (3xTF32,
+    bias and ReLU in its epilogue) whenever x meets TMA's alignment rules, else on the library GEMM;
+    the weight / bias gradient (a reduction over all nodes with a tiny output) runs on the split-K
+    kernel dgmc_wgrad when the output is small, else stays with the library."""
+    if x.is_cuda and x.dtype == torch.float32 and x.dim() == 2 and x.stride(1) == 1 \
+            and weight.dtype == torch.float32 and (bias is not None or not relu):
         group = None
         if key is not None and _DEFER[0] is not None and torch.is_grad_enabled():
             group = _DEFER[0].setdefault((key, x.size(0), tuple(weight.shape)), WGradGroup())
-        return _NodeLinear.apply(x, weight, bias, relu, group)
-    y = torch.nn.functional.linear(x, weight, bias)
+        return _NodeLinear.apply(x, weight, bias, relu, group, kn)
+    y = torch.addmm(bias, x, weight) if (kn and bias is not None) else (
+        x @ weight if kn else torch.nn.functional.linear(x, weight, bias))
     return torch.relu(y) if relu else y
 
 

@@ -207,6 +207,22 @@ int dgmc_wgrad_tc_splits(int64_t k, int m, int n);
 int dgmc_wgrad_tc_partial(const float* g, int64_t ldg, const float* x, int64_t ldx, int64_t k, int m, int n,
                           float* partial, float* partial_b, dgmc_stream_t stream);
 
+/* ---- per-node linear map on the tensor cores ------------------------------------------------
+ * y[rows, n_out] = relu?(x[rows, k_in] w[n_out, k_in]^T + bias): the GEMM inside every RelConv
+ * (rel.py:27-30 after hoisting the aggregation), SplineConv (spline.py:40-47), Lin (rel.py:66 /
+ * spline.py:71) and the first MLP layer of dgmc.py:62-66; with the transposed weight it is also
+ * their input gradient.  tcgen05 kind::tf32 with hi/lo operand splitting (three MMAs per product,
+ * fp32 TMEM accumulator; ~2^-21 relative, i.e. fp32-level).  Two calls: the weight is split once
+ * into the workspace (transposed = 1 reads w as [k_in, n_out], for dx = g w), then any number of
+ * dgmc_linear_tc calls use that workspace.  x needs a 16-byte aligned base and pitch
+ * (dgmc_linear_tc_supported); Inf inputs produce NaN (Inf - Inf in the split). */
+int dgmc_linear_tc_supported(int64_t rows, int n_out, int k_in, int64_t ldx, const float* x);
+size_t dgmc_linear_tc_workspace(int n_out, int k_in);
+int dgmc_linear_tc_split_weight(const float* w, int64_t ldw, int transposed, int n_out, int k_in,
+                                void* workspace, size_t workspace_bytes, dgmc_stream_t stream);
+int dgmc_linear_tc(const float* x, int64_t ldx, const void* split_weight, const float* bias, int relu,
+                   float* y, int64_t ldy, int64_t rows, int n_out, int k_in, dgmc_stream_t stream);
+
 /* ---- dense branch: consensus update without materialising D [B, N_s, N_t, R] ----------------
  * s_out[b,i,j] = s_in[b,i,j] + [s_mask[b,i] & t_mask[b,j]] * (b2 + sum_c w2[c] relu(ps[b,i,c] - pt[b,j,c]))
  * replaces D = o_s[:, :, None] - o_t[:, None], mlp(D).masked_fill(~S_mask, 0) at dgmc.py:178-179
