@@ -1,8 +1,9 @@
 // Per-node linear map  Y[rows, n_out] = act(X[rows, k_in] W[n_out, k_in]^T + bias)  on the 5th-gen
 // tensor cores with fp32-level accuracy ("3xTF32"): X = X_hi + X_lo and W = W_hi + W_lo with hi = the
 // top 19 bits of the fp32 value (exactly what kind::tf32 reads) and lo = x - hi; the product is
-// accumulated as X_hi W_hi + X_hi W_lo + X_lo W_hi in the fp32 TMEM accumulator (the dropped lo*lo
-// term and the truncation of lo are ~2^-21 relative).  This is the GEMM behind every RelConv /
+// accumulated as X_hi W_hi + X_hi W_lo + X_lo W_hi in fp32 TMEM accumulators (the dropped lo*lo
+// term and the truncation of lo are ~2^-21 relative; measured error against fp64 = that of the
+// library's IEEE fp32 SGEMM, tests/test_gpu_linear_tc.py).  This is the GEMM behind every RelConv /
 // SplineConv / Lin layer of psi_1 and psi_2 (rel.py:27-30, spline.py:40-47, mlp.py) and, with the
 // transposed weight, their input gradient; the library SGEMM runs those on the FFMA pipe at ~40
 // TFLOP/s.
@@ -12,13 +13,15 @@
 // on the fly.  One CTA per 128-row x BN-column tile, 6 warps:
 //   warp 0      TMA producer: per 32-wide k block, X[128 x 32] (raw fp32), W_hi[BN x 32], W_lo[BN x 32]
 //               -> 128-byte-swizzled shared-memory stage, mbarrier complete_tx
-//   warps 2-5   split the raw X tile in place into hi (same position) and lo (second buffer, same
-//               swizzled position, so no address math), fence.proxy.async, arrive
-//   warp 1      one thread issues 4 (k8 steps) x 3 tcgen05.mma.kind::tf32 (M=128, N=BN, K=8) per
-//               stage; tcgen05.commit releases the stage to the producer
-//   warps 2-5   epilogue: tcgen05.ld of the accumulator rows, + bias, ReLU, 128-bit stores
+//   warps 2-5   write lo = x - hi of the raw X tile into a second buffer (same swizzled position,
+//               so no address math), fence.proxy.async, arrive.  The raw tile itself is the hi
+//               operand: kind::tf32 ignores the low 13 mantissa bits (measured: bit-identical
+//               results with and without masking them first)
+//   warp 1      one thread issues, per k8 step, X_hi x [W_hi ; W_lo] (N = 2 BN) and X_lo x W_hi
+//               (N = BN) as tcgen05.mma.kind::tf32; tcgen05.commit releases the stage to the producer
+//   warps 2-5   epilogue: tcgen05.ld of the accumulator rows (summing the accumulator pairs),
+//               + bias, ReLU, 128-bit stores
 // Rows and k beyond the matrix are zero-filled by TMA (X) or by the padded workspace (W).
-#include <cstdlib>
 #include "common.cuh"
 #include "tc_common.cuh"
 #include "../../include/dgmc_b200.h"
@@ -56,7 +59,7 @@ __global__ void __launch_bounds__(LT_THREADS)
 linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_whi,
                  const __grid_constant__ CUtensorMap map_wlo, const float* __restrict__ bias, int relu,
                  float* __restrict__ y, long long ldy, long long rows, int n_out, int k_blocks,
-                 int n_stages, int rewrite_hi) {
+                 int n_stages) {
     constexpr int B_BYTES = BN * LT_KB * 4;
     constexpr int STAGE_BYTES = 2 * LT_A_BYTES + 2 * B_BYTES;
     extern __shared__ uint8_t smem_raw[];
@@ -151,13 +154,12 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
 #pragma unroll
             for (int i = 0; i < LT_A_BYTES / 16 / 128; ++i) {
                 const float4 v = a_hi[t + i * 128];
-                float4 h, l;
-                h.x = __uint_as_float(__float_as_uint(v.x) & 0xffffe000u); l.x = v.x - h.x;
-                h.y = __uint_as_float(__float_as_uint(v.y) & 0xffffe000u); l.y = v.y - h.y;
-                h.z = __uint_as_float(__float_as_uint(v.z) & 0xffffe000u); l.z = v.z - h.z;
-                h.w = __uint_as_float(__float_as_uint(v.w) & 0xffffe000u); l.w = v.w - h.w;
-                if (rewrite_hi) a_hi[t + i * 128] = h;
-                a_lo[t + i * 128] = l;
+                float4 l;
+                l.x = v.x - __uint_as_float(__float_as_uint(v.x) & 0xffffe000u);
+                l.y = v.y - __uint_as_float(__float_as_uint(v.y) & 0xffffe000u);
+                l.z = v.z - __uint_as_float(__float_as_uint(v.z) & 0xffffe000u);
+                l.w = v.w - __uint_as_float(__float_as_uint(v.w) & 0xffffe000u);
+                a_lo[t + i * 128] = l;   // the raw tile itself serves as X_hi
             }
             fence_proxy_async_smem();     // st.shared above -> UMMA operand reads
             __syncwarp();
@@ -280,8 +282,7 @@ static int lt_launch(const CUtensorMap& mx, const CUtensorMap& mh, const CUtenso
     }
     dim3 grid(n_pad / BN, (unsigned)((rows + LT_BM - 1) / LT_BM));
     linear_tc_kernel<BN><<<grid, LT_THREADS, smem, stream>>>(mx, mh, ml, bias, relu, y, ldy, rows, n_out,
-                                                            k_blocks, n_stages,
-                                                            getenv("DGMC_LT_RAW_HI") ? 0 : 1);
+                                                            k_blocks, n_stages);
     return DGMC_OK;
 }
 

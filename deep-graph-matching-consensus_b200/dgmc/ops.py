@@ -391,7 +391,7 @@ def region_cached(key, make):
     return region[slot]
 
 
-LINEAR_TENSOR_CORE = False  # forward / input-gradient GEMMs on dgmc_linear_tc (tcgen05, 3xTF32); off until validated end to end
+LINEAR_TENSOR_CORE = True   # forward / input-gradient GEMMs on dgmc_linear_tc (tcgen05, 3xTF32)
 
 
 def _linear_tc_ok(x, n_out, k_in):
