@@ -1,8 +1,8 @@
 // Per-node linear map  Y[rows, n_out] = act(X[rows, k_in] W[n_out, k_in]^T + bias)  on the 5th-gen
-// tensor cores with fp32-level accuracy ("3xTF32"): X = X_hi + X_lo and W = W_hi + W_lo with hi = the
-// top 19 bits of the fp32 value (exactly what kind::tf32 reads) and lo = x - hi; the product is
-// accumulated as X_hi W_hi + X_hi W_lo + X_lo W_hi in fp32 TMEM accumulators (the dropped lo*lo
-// term and the truncation of lo are ~2^-21 relative; measured error against fp64 = that of the
+// tensor cores with fp32-level accuracy ("3xTF32"): X = X_hi + X_lo and W = W_hi + W_lo with hi = x
+// rounded to tf32 (19 bits) and lo = x - hi rounded to tf32; the product is accumulated as
+// X_hi W_hi + X_hi W_lo + X_lo W_hi in fp32 TMEM accumulators (the dropped lo*lo term and the
+// rounding of lo are ~2^-24 relative and zero-mean; measured error against fp64 = that of the
 // library's IEEE fp32 SGEMM, tests/test_gpu_linear_tc.py).  This is the GEMM behind every RelConv /
 // SplineConv / Lin layer of psi_1 and psi_2 (rel.py:27-30, spline.py:40-47, mlp.py) and, with the
 // transposed weight, their input gradient; the library SGEMM runs those on the FFMA pipe at ~40
@@ -13,10 +13,8 @@
 // on the fly.  One CTA per 128-row x BN-column tile, 6 warps:
 //   warp 0      TMA producer: per 32-wide k block, X[128 x 32] (raw fp32), W_hi[BN x 32], W_lo[BN x 32]
 //               -> 128-byte-swizzled shared-memory stage, mbarrier complete_tx
-//   warps 2-5   write lo = x - hi of the raw X tile into a second buffer (same swizzled position,
-//               so no address math), fence.proxy.async, arrive.  The raw tile itself is the hi
-//               operand: kind::tf32 ignores the low 13 mantissa bits (measured: bit-identical
-//               results with and without masking them first)
+//   warps 2-5   split the raw X tile into hi (in place) and lo (second buffer, same swizzled
+//               position, so no address math), fence.proxy.async, arrive
 //   warp 1      one thread issues, per k8 step, X_hi x [W_hi ; W_lo] (N = 2 BN) and X_lo x W_hi
 //               (N = BN) as tcgen05.mma.kind::tf32; tcgen05.commit releases the stage to the producer
 //   warps 2-5   epilogue: tcgen05.ld of the accumulator rows (summing the accumulator pairs),
@@ -36,6 +34,19 @@ constexpr int LT_THREADS = 192;
 constexpr int LT_MAX_STAGES = 6;
 constexpr int LT_ACC = 2;                     // accumulator pairs [H | L] the k8 steps alternate between
 
+// x = hi + lo + O(2^-24 x) with hi and lo both EXACT tf32 values (round to nearest, so that the
+// tensor core's operand truncation is a no-op).  Rounding - not truncating - matters: truncated
+// parts all err towards zero, which biases every product the same way; such an error does not
+// average out over the reduction (measured: gradients 100x further from fp64 than with IEEE fp32),
+// whereas the rounded split is zero-mean and ends up at fp32 level.
+__device__ __forceinline__ float round_tf32(float v) {
+    return __uint_as_float((__float_as_uint(v) + 0x1000u) & 0xffffe000u);
+}
+__device__ __forceinline__ void split_rn(float v, float& hi, float& lo) {
+    hi = round_tf32(v);
+    lo = round_tf32(v - hi);
+}
+
 __global__ void __launch_bounds__(256) split_weight_kernel(const float* __restrict__ w, long long ldw,
                                                            int trans, int n_out, int k_in, int n_pad,
                                                            int k_pad, float* __restrict__ hi,
@@ -48,9 +59,10 @@ __global__ void __launch_bounds__(256) split_weight_kernel(const float* __restri
         const int k = trans ? (int)(i / n_pad) : (int)(i % k_pad);
         float v = 0.f;
         if (n < n_out && k < k_in) v = trans ? __ldg(w + (long long)k * ldw + n) : __ldg(w + (long long)n * ldw + k);
-        const float h = __uint_as_float(__float_as_uint(v) & 0xffffe000u);
+        float h, l;
+        split_rn(v, h, l);
         hi[(size_t)n * k_pad + k] = h;
-        lo[(size_t)n * k_pad + k] = v - h;
+        lo[(size_t)n * k_pad + k] = l;
     }
 }
 
@@ -154,12 +166,11 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
 #pragma unroll
             for (int i = 0; i < LT_A_BYTES / 16 / 128; ++i) {
                 const float4 v = a_hi[t + i * 128];
-                float4 l;
-                l.x = v.x - __uint_as_float(__float_as_uint(v.x) & 0xffffe000u);
-                l.y = v.y - __uint_as_float(__float_as_uint(v.y) & 0xffffe000u);
-                l.z = v.z - __uint_as_float(__float_as_uint(v.z) & 0xffffe000u);
-                l.w = v.w - __uint_as_float(__float_as_uint(v.w) & 0xffffe000u);
-                a_lo[t + i * 128] = l;   // the raw tile itself serves as X_hi
+                float4 h, l;
+                split_rn(v.x, h.x, l.x); split_rn(v.y, h.y, l.y);
+                split_rn(v.z, h.z, l.z); split_rn(v.w, h.w, l.w);
+                a_hi[t + i * 128] = h;
+                a_lo[t + i * 128] = l;
             }
             fence_proxy_async_smem();     // st.shared above -> UMMA operand reads
             __syncwarp();

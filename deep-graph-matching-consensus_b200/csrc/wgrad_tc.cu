@@ -1,7 +1,7 @@
 // Weight gradient dW[m, n] = sum_k G[k, m] X[k, n] on the 5th-gen tensor cores with fp32-level
-// accuracy ("3xTF32"): every fp32 operand is split into hi = its top 19 bits (what kind::tf32 reads)
-// and lo = x - hi, and the product is accumulated as hi*hi + hi*lo + lo*hi in the fp32 TMEM
-// accumulator (the dropped lo*lo term and the truncation of lo are ~2^-21 relative).  Used for the
+// accuracy ("3xTF32"): every fp32 operand is split into hi = x rounded to tf32 (19 bits) and
+// lo = x - hi rounded to tf32, and the product is accumulated as hi*hi + hi*lo + lo*hi in the fp32
+// TMEM accumulator (the dropped lo*lo term and the rounding of lo are ~2^-24 relative, zero-mean).  Used for the
 // BACKWARD pass only: gradients carry a 5e-4 tolerance, the forward GEMMs that decide S_L stay in
 // IEEE fp32 (library SGEMM).
 //
@@ -33,8 +33,10 @@ __device__ __forceinline__ uint32_t sw128_offset(int row, int k) {
 }
 
 __device__ __forceinline__ void split_tf32(float v, float& hi, float& lo) {
-    hi = __uint_as_float(__float_as_uint(v) & 0xffffe000u);
-    lo = v - hi;
+    // round (not truncate) both parts to tf32: truncation errs towards zero in every product, a
+    // bias that does not average out over the reduction (see linear_tc.cu)
+    hi = __uint_as_float((__float_as_uint(v) + 0x1000u) & 0xffffe000u);
+    lo = __uint_as_float((__float_as_uint(v - hi) + 0x1000u) & 0xffffe000u);
 }
 
 __global__ void __launch_bounds__(WT_THREADS, 2)

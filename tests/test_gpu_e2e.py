@@ -36,11 +36,14 @@ def test_golden_case(name):
         assert got['hits3_L'] == pytest.approx(ref64['hits3_L'].item())
     if 'grads' in ref64:
         assert set(got['grads']) == set(ref64['grads'])
+        # floor: parameters whose true gradient is a sum of cancelling terms (the bias in front of a
+        # softmax: exactly 0) carry the rounding of those terms, up to 5e-5 of the model's largest gradient
+        gmax = max(g.abs().max().item() for g in ref64['grads'].values())
         for k, g in ref64['grads'].items():
             scale = g.abs().max().item()
             err = (got['grads'][k].double().cpu() - g).abs().max().item()
             noise = (ref32['grads'][k].double() - g).abs().max().item()
-            assert err <= max(5e-4 * scale, 5 * noise) + 1e-9, \
+            assert err <= max(5e-4 * scale, 5 * noise, 5e-5 * gmax) + 1e-9, \
                 'grad %s: err %.3g, scale %.3g, ref fp32 noise %.3g' % (k, err, scale, noise)
 
 

@@ -83,19 +83,9 @@ def test_dbp15k_lite_sparse_training_step_against_oracle():
                 continue
             scale = gref.abs().max().item()
             noise = (ref32['grads'][n].double() - gref).abs().max().item()
-            d = (got[n].grad.double().cpu() - gref).abs()
-            # Typical entry: 2e-5 of the tensor's own scale (+ 2e-6 of the model's largest gradient
-            # for tensors whose true gradient is ~0).  Outliers: a ReLU unit whose pre-activation
-            # is within rounding of zero takes the other branch under ANY change of summation
-            # order (measured with the library SGEMM and with the tensor-core GEMM alike, on
-            # different seeds); one flipped unit moves one row of a weight gradient by ~1/N_nodes
-            # of the model's gradient scale.  So: at most two rows (output channels) of a tensor, or
-            # 2 % of its entries, may exceed the tight bound, and none may exceed 1e-3 of the
-            # largest gradient.
-            tight = 2e-5 * scale + 2e-6 * gmax + 5 * noise
-            outliers = max(0.02, 2.5 / gref.size(0))
-            assert (d > tight).double().mean().item() <= outliers, (n, d.max().item(), scale, noise)
-            assert d.max().item() <= max(1e-3 * gmax, tight), (n, d.max().item(), scale, gmax)
+            err = (got[n].grad.double().cpu() - gref).abs().max().item()
+            # 5e-5 * gmax: floor for parameters whose true gradient cancels to ~0 (see test_gpu_e2e)
+            assert err <= max(5e-4 * scale, 5 * noise, 5e-5 * gmax) + 1e-9, (n, err, scale, noise)
 
 
 def test_pascal_shaped_ragged_dense_batch_against_oracle():
