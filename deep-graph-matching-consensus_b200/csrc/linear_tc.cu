@@ -10,16 +10,18 @@
 //
 // W is small (<= a few MB): a prologue kernel splits (and, for the input gradient, transposes) it
 // ONCE into K-major, zero-padded hi / lo copies in the caller's workspace.  X is large and is split
-// on the fly.  One CTA per 128-row x BN-column tile, 6 warps:
+// on the fly.  Persistent kernel, one CTA per SM looping over 128-row x BN-column tiles, 10 warps:
 //   warp 0      TMA producer: per 32-wide k block, X[128 x 32] (raw fp32), W_hi[BN x 32], W_lo[BN x 32]
 //               -> 128-byte-swizzled shared-memory stage, mbarrier complete_tx
 //   warps 2-5   split the raw X tile into hi (in place) and lo (second buffer, same swizzled
 //               position, so no address math), fence.proxy.async, arrive
 //   warp 1      one thread issues, per k8 step, X_hi x [W_hi ; W_lo] (N = 2 BN) and X_lo x W_hi
 //               (N = BN) as tcgen05.mma.kind::tf32; tcgen05.commit releases the stage to the producer
-//   warps 2-5   epilogue: tcgen05.ld of the accumulator rows (summing the accumulator pairs),
-//               + bias, ReLU, 128-bit stores
+//   warps 6-9   epilogue: tcgen05.ld of the accumulator rows (summing the accumulator pairs),
+//               + bias, ReLU, swizzled staging rows, one TMA store per 32 x 32 box; at BN = 64 there are two accumulator sets, so the
+//               epilogue of one tile overlaps the MMAs of the next
 // Rows and k beyond the matrix are zero-filled by TMA (X) or by the padded workspace (W).
+#include <cstring>
 #include "common.cuh"
 #include "tc_common.cuh"
 #include "../../include/dgmc_b200.h"
@@ -30,9 +32,11 @@ namespace tc {
 constexpr int LT_BM = 128;                    // rows per tile (UMMA M)
 constexpr int LT_KB = 32;                     // k per stage = one 128-byte swizzled row of fp32
 constexpr int LT_A_BYTES = LT_BM * LT_KB * 4; // 16 KB
-constexpr int LT_THREADS = 192;
+constexpr int LT_THREADS = 320;                // producer, MMA issuer, 4 split warps, 4 epilogue warps
 constexpr int LT_MAX_STAGES = 6;
-constexpr int LT_ACC = 2;                     // accumulator pairs [H | L] the k8 steps alternate between
+constexpr int LT_TMEM_COLS = 512;
+constexpr int LT_OUT_BYTES = 32 * 128;         // epilogue staging per warp: 32 rows x 32 fp32, 128-byte swizzled
+__host__ __device__ constexpr int lt_stages(int bn) { return bn == 64 ? 4 : 3; }   // 4 x 48 KB / 3 x 64 KB
 
 // x = hi + lo + O(2^-24 x) with hi and lo both EXACT tf32 values (round to nearest, so that the
 // tensor core's operand truncation is a no-op).  Rounding - not truncating - matters: truncated
@@ -66,39 +70,45 @@ __global__ void __launch_bounds__(256) split_weight_kernel(const float* __restri
     }
 }
 
-template <int BN>
-__global__ void __launch_bounds__(LT_THREADS)
+// LT_ACC: accumulator pairs [H | L] the k8 steps alternate between (2 for long reductions, see the
+// MMA issuer; 1 for k_in <= 128, which leaves room for a second accumulator set at BN = 128)
+template <int BN, int LT_ACC>
+__global__ void __launch_bounds__(LT_THREADS, 1)
 linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_whi,
-                 const __grid_constant__ CUtensorMap map_wlo, const float* __restrict__ bias, int relu,
-                 float* __restrict__ y, long long ldy, long long rows, int n_out, int k_blocks,
-                 int n_stages) {
+                 const __grid_constant__ CUtensorMap map_wlo, const __grid_constant__ CUtensorMap map_y,
+                 int y_tma, const float* __restrict__ bias, int relu, float* __restrict__ y, long long ldy,
+                 long long rows, int n_out, int k_blocks, int n_tiles_n, int n_tiles) {
     constexpr int B_BYTES = BN * LT_KB * 4;
     constexpr int STAGE_BYTES = 2 * LT_A_BYTES + 2 * B_BYTES;
+    constexpr int NSTAGE = lt_stages(BN);
+    constexpr int ACC_COLS = 2 * LT_ACC * BN;          // one accumulator set: LT_ACC pairs [H | L]
+    // accumulator sets: with two, the epilogue of one tile overlaps the MMAs of the next
+    constexpr int NBUF = LT_TMEM_COLS / ACC_COLS >= 2 ? 2 : 1;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)n_stages * STAGE_BYTES);
+    uint8_t* out_stage = smem + (size_t)NSTAGE * STAGE_BYTES;      // 4 epilogue warps x [32 rows x 128 B]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(out_stage + 4 * LT_OUT_BYTES);
     uint64_t* full = bars;                          // TMA bytes landed
     uint64_t* split_done = bars + LT_MAX_STAGES;    // X tile split into hi / lo (4 warp arrivals)
     uint64_t* empty = bars + 2 * LT_MAX_STAGES;     // MMAs of the stage retired
-    uint64_t* acc_full = bars + 3 * LT_MAX_STAGES;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_full + 1);
+    uint64_t* acc_full = bars + 3 * LT_MAX_STAGES;  // [2] accumulator set complete (tcgen05.commit)
+    uint64_t* acc_empty = acc_full + 2;             // [2] drained by the 4 epilogue warps
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int n0 = blockIdx.x * BN;
-    const long long m0 = (long long)blockIdx.y * LT_BM;
 
     if (warp == 0 && lane == 0) {
-        for (int s = 0; s < n_stages; ++s) {
+        for (int s = 0; s < NSTAGE; ++s) {
             mbar_init(&full[s], 1);
             mbar_init(&split_done[s], 4);
             mbar_init(&empty[s], 1);
         }
-        mbar_init(acc_full, 1);
+        for (int b = 0; b < 2; ++b) { mbar_init(&acc_full[b], 1); mbar_init(&acc_empty[b], 4); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
-                         smem_u32(tmem_slot)), "r"(2 * LT_ACC * BN));
+                         smem_u32(tmem_slot)), "r"(LT_TMEM_COLS));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
     }
     tcgen05_fence_before();
@@ -106,18 +116,25 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     tcgen05_fence_after();
     const uint32_t tmem_d = *tmem_slot;
 
+    // Persistent: CTA b works on tiles b, b + grid, ...; consecutive tiles are the column tiles of one
+    // row block, so CTAs running side by side share their X rows in L2.  The shared-memory ring
+    // runs on across tile boundaries: the loads of the next tile are in flight while this one's
+    // MMAs and epilogue finish.
     if (warp == 0) {
         if (lane == 0) {
             // ================= TMA producer =================
             int s = 0; uint32_t phase = 0;
-            for (int kb = 0; kb < k_blocks; ++kb) {
-                mbar_wait(&empty[s], phase ^ 1u);
-                uint8_t* st = smem + (size_t)s * STAGE_BYTES;
-                mbar_expect_tx(&full[s], (uint32_t)(LT_A_BYTES + 2 * B_BYTES));
-                tma_load_2d(st, &map_x, &full[s], kb * LT_KB, (int)m0);
-                tma_load_2d(st + 2 * LT_A_BYTES, &map_whi, &full[s], kb * LT_KB, n0);
-                tma_load_2d(st + 2 * LT_A_BYTES + B_BYTES, &map_wlo, &full[s], kb * LT_KB, n0);
-                if (++s == n_stages) { s = 0; phase ^= 1u; }
+            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+                const int m0 = (tile / n_tiles_n) * LT_BM, n0 = (tile % n_tiles_n) * BN;
+                for (int kb = 0; kb < k_blocks; ++kb) {
+                    mbar_wait(&empty[s], phase ^ 1u);
+                    uint8_t* st = smem + (size_t)s * STAGE_BYTES;
+                    mbar_expect_tx(&full[s], (uint32_t)(LT_A_BYTES + 2 * B_BYTES));
+                    tma_load_2d(st, &map_x, &full[s], kb * LT_KB, m0);
+                    tma_load_2d(st + 2 * LT_A_BYTES, &map_whi, &full[s], kb * LT_KB, n0);
+                    tma_load_2d(st + 2 * LT_A_BYTES + B_BYTES, &map_wlo, &full[s], kb * LT_KB, n0);
+                    if (++s == NSTAGE) { s = 0; phase ^= 1u; }
+                }
             }
         }
     } else if (warp == 1) {
@@ -135,105 +152,136 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                                             ((uint32_t)((2 * BN) >> 3) << 17) | ((uint32_t)(LT_BM >> 4) << 24);
             constexpr uint32_t idesc_lo = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) |
                                           ((uint32_t)(LT_BM >> 4) << 24);
-            int s = 0; uint32_t phase = 0; int step = 0;
-            for (int kb = 0; kb < k_blocks; ++kb) {
-                mbar_wait(&full[s], phase);          // W tiles (written by TMA)
-                mbar_wait(&split_done[s], phase);    // X tiles (rewritten by warps 2-5)
+            int s = 0; uint32_t phase = 0; int it = 0;
+            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+                const int buf = it % NBUF, use = it / NBUF;
+                mbar_wait(&acc_empty[buf], (uint32_t)((use & 1) ^ 1));   // epilogue has drained this set
                 tcgen05_fence_after();
-                const uint32_t st = smem_u32(smem + (size_t)s * STAGE_BYTES);
-                const uint64_t d_ahi = umma_desc_sw128(st), d_alo = umma_desc_sw128(st + LT_A_BYTES);
-                const uint64_t d_b = umma_desc_sw128(st + 2 * LT_A_BYTES);   // W_hi rows, then W_lo rows
+                const uint32_t acc = tmem_d + (uint32_t)(buf * ACC_COLS);
+                int step = 0;
+                for (int kb = 0; kb < k_blocks; ++kb) {
+                    mbar_wait(&full[s], phase);          // W tiles (written by TMA)
+                    mbar_wait(&split_done[s], phase);    // X tiles (rewritten by warps 2-5)
+                    tcgen05_fence_after();
+                    const uint32_t st = smem_u32(smem + (size_t)s * STAGE_BYTES);
+                    const uint64_t d_ahi = umma_desc_sw128(st), d_alo = umma_desc_sw128(st + LT_A_BYTES);
+                    const uint64_t d_b = umma_desc_sw128(st + 2 * LT_A_BYTES);   // W_hi rows, then W_lo rows
 #pragma unroll
-                for (int ks = 0; ks < LT_KB / 8; ++ks, ++step) {   // +32 bytes per K=8 step inside the swizzled row
-                    const uint64_t o = (uint64_t)(2 * ks);
-                    const uint32_t d = tmem_d + (uint32_t)((step % LT_ACC) * 2 * BN);
-                    tcgen05_mma_tf32(d, d_ahi + o, d_b + o, idesc_wide, (uint32_t)(step >= LT_ACC));
-                    tcgen05_mma_tf32(d + BN, d_alo + o, d_b + o, idesc_lo, 1u);
+                    for (int ks = 0; ks < LT_KB / 8; ++ks, ++step) {   // +32 bytes per K=8 step inside the swizzled row
+                        const uint64_t o = (uint64_t)(2 * ks);
+                        const uint32_t d = acc + (uint32_t)((step % LT_ACC) * 2 * BN);
+                        tcgen05_mma_tf32(d, d_ahi + o, d_b + o, idesc_wide, (uint32_t)(step >= LT_ACC));
+                        tcgen05_mma_tf32(d + BN, d_alo + o, d_b + o, idesc_lo, 1u);
+                    }
+                    tcgen05_commit(&empty[s]);
+                    if (++s == NSTAGE) { s = 0; phase ^= 1u; }
                 }
-                tcgen05_commit(&empty[s]);
-                if (++s == n_stages) { s = 0; phase ^= 1u; }
+                tcgen05_commit(&acc_full[buf]);
             }
-            tcgen05_commit(acc_full);
         }
-    } else {
-        // ================= split X in place, then epilogue =================
+    } else if (warp < 6) {
+        // ================= split X into hi (in place) and lo =================
         const int t = threadIdx.x - 64;               // 0..127
         int s = 0; uint32_t phase = 0;
-        for (int kb = 0; kb < k_blocks; ++kb) {
-            mbar_wait(&full[s], phase);
-            float4* a_hi = reinterpret_cast<float4*>(smem + (size_t)s * STAGE_BYTES);
-            float4* a_lo = a_hi + LT_A_BYTES / 16;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            for (int kb = 0; kb < k_blocks; ++kb) {
+                mbar_wait(&full[s], phase);
+                float4* a_hi = reinterpret_cast<float4*>(smem + (size_t)s * STAGE_BYTES);
+                float4* a_lo = a_hi + LT_A_BYTES / 16;
 #pragma unroll
-            for (int i = 0; i < LT_A_BYTES / 16 / 128; ++i) {
-                const float4 v = a_hi[t + i * 128];
-                float4 h, l;
-                split_rn(v.x, h.x, l.x); split_rn(v.y, h.y, l.y);
-                split_rn(v.z, h.z, l.z); split_rn(v.w, h.w, l.w);
-                a_hi[t + i * 128] = h;
-                a_lo[t + i * 128] = l;
-            }
-            fence_proxy_async_smem();     // st.shared above -> UMMA operand reads
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&split_done[s]);
-            if (++s == n_stages) { s = 0; phase ^= 1u; }
-        }
-        mbar_wait(acc_full, 0);
-        tcgen05_fence_after();
-        const int quarter = warp & 3;                  // TMEM lanes this warp may read
-        const long long row = m0 + quarter * 32 + lane;
-        const bool vec = (ldy % 4 == 0) && ((reinterpret_cast<uintptr_t>(y) & 15) == 0);
-#pragma unroll 1
-        for (int cb = 0; cb < BN; cb += 32) {
-            if (n0 + cb >= n_out) break;               // warp-uniform
-            float r[32], q[32];
-            const uint32_t lane_base = tmem_d + ((uint32_t)(quarter * 32) << 16) + (uint32_t)cb;
-            tmem_ld_32x32b_x32(lane_base, r);                                   // H_0
-#pragma unroll
-            for (int p = 1; p < LT_ACC; ++p) {                                  // + H_1 ...
-                tmem_ld_32x32b_x32(lane_base + (uint32_t)(p * 2 * BN), q);
-#pragma unroll
-                for (int j = 0; j < 32; ++j) r[j] += q[j];
-            }
-            {                                                                   // + (L_0 + L_1 ...)
-                float l[32];
-                tmem_ld_32x32b_x32(lane_base + (uint32_t)BN, l);
-#pragma unroll
-                for (int p = 1; p < LT_ACC; ++p) {
-                    tmem_ld_32x32b_x32(lane_base + (uint32_t)(p * 2 * BN + BN), q);
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) l[j] += q[j];
+                for (int i = 0; i < LT_A_BYTES / 16 / 128; ++i) {
+                    const float4 v = a_hi[t + i * 128];
+                    float4 h, l;
+                    split_rn(v.x, h.x, l.x); split_rn(v.y, h.y, l.y);
+                    split_rn(v.z, h.z, l.z); split_rn(v.w, h.w, l.w);
+                    a_hi[t + i * 128] = h;
+                    a_lo[t + i * 128] = l;
                 }
-#pragma unroll
-                for (int j = 0; j < 32; ++j) r[j] += l[j];
+                fence_proxy_async_smem();     // st.shared above -> UMMA operand reads
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&split_done[s]);
+                if (++s == NSTAGE) { s = 0; phase ^= 1u; }
             }
-            const int c0 = n0 + cb;
-            if (bias) {
+        }
+    } else {
+        // ================= epilogue (warps 6-9) =================
+        const int quarter = warp & 3;                  // TMEM lanes this warp may read
+        uint8_t* my_stage = out_stage + (warp - 6) * LT_OUT_BYTES;
+        int it = 0;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+            const int buf = it % NBUF, use = it / NBUF;
+            const long long m0 = (long long)(tile / n_tiles_n) * LT_BM;
+            const int n0 = (tile % n_tiles_n) * BN;
+            mbar_wait(&acc_full[buf], (uint32_t)(use & 1));
+            tcgen05_fence_after();
+            const long long row0 = m0 + quarter * 32, row = row0 + lane;
+#pragma unroll 1
+            for (int cb = 0; cb < BN; cb += 32) {
+                if (n0 + cb >= n_out) break;               // warp-uniform; cb = 0 is always live
+                float r[32];
+                {
+                    const uint32_t lane_base = tmem_d + ((uint32_t)(quarter * 32) << 16) +
+                                               (uint32_t)(buf * ACC_COLS + cb);
+                    float l[32];
+                    tmem_ld_32x32b_x32_pair(lane_base, lane_base + (uint32_t)BN, r, l);      // H_0, L_0
+                    if (LT_ACC == 2) {
+                        float q[32], m[32];
+                        tmem_ld_32x32b_x32_pair(lane_base + (uint32_t)(2 * BN), lane_base + (uint32_t)(3 * BN), q, m);
 #pragma unroll
-                for (int j = 0; j < 32; ++j) r[j] += (c0 + j < n_out) ? __ldg(bias + c0 + j) : 0.f;
-            }
-            if (relu) {
+                        for (int j = 0; j < 32; ++j) { r[j] += q[j]; l[j] += m[j]; }         // + H_1, + L_1
+                    }
 #pragma unroll
-                for (int j = 0; j < 32; ++j) r[j] = fmaxf(r[j], 0.f);
-            }
-            if (row < rows) {
-                float* dst = y + row * ldy + c0;
-                if (vec && c0 + 32 <= n_out) {
+                    for (int j = 0; j < 32; ++j) r[j] += l[j];
+                }
+                if (cb + 32 >= BN || n0 + cb + 32 >= n_out) {
+                    // last chunk read: the MMA warp may overwrite this accumulator set while the
+                    // stores below drain
+                    tcgen05_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&acc_empty[buf]);
+                }
+                const int c0 = n0 + cb;
+                if (bias) {
 #pragma unroll
-                    for (int j = 0; j < 32; j += 4)
-                        *reinterpret_cast<float4*>(dst + j) = make_float4(r[j], r[j + 1], r[j + 2], r[j + 3]);
-                } else {
+                    for (int j = 0; j < 32; ++j) r[j] += (c0 + j < n_out) ? __ldg(bias + c0 + j) : 0.f;
+                }
+                if (relu) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) r[j] = fmaxf(r[j], 0.f);
+                }
+                if (y_tma) {
+                    // registers -> swizzled staging rows (conflict-free 128-bit stores) -> one TMA
+                    // store of the 32 x 32 box, which writes whole 128-byte row segments and clips
+                    // rows / columns beyond the matrix
+                    if (row0 < rows) {
+                        if (lane == 0) tma_store_wait_read();
+                        __syncwarp();
+#pragma unroll
+                        for (int j = 0; j < 8; ++j)
+                            *reinterpret_cast<float4*>(my_stage + lane * 128 + ((j ^ (lane & 7)) << 4)) =
+                                make_float4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+                        fence_proxy_async_smem();
+                        __syncwarp();
+                        if (lane == 0) {
+                            tma_store_2d(&map_y, my_stage, c0, (int)row0);
+                            tma_store_commit();
+                        }
+                    }
+                } else if (row < rows) {
+                    float* dst = y + row * ldy + c0;
 #pragma unroll
                     for (int j = 0; j < 32; ++j)
                         if (c0 + j < n_out) dst[j] = r[j];
                 }
             }
         }
+        if (lane == 0) tma_store_wait_all();
     }
     tcgen05_fence_before();
     __syncthreads();
     if (warp == 1) {
         tcgen05_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(2 * LT_ACC * BN));
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(LT_TMEM_COLS));
     }
 }
 
@@ -257,6 +305,7 @@ static EncodeTiledFnL lt_encode_tiled() {
 // fp32 [rows x cols] row-major with pitch ld (floats); box = 32 columns x box_rows rows
 static int lt_make_map(CUtensorMap* map, const void* base, long long rows, long long cols, long long ld,
                        int box_rows) {
+    memset(map, 0, sizeof(*map));
     EncodeTiledFnL enc = lt_encode_tiled();
     if (!enc) { set_error("linear_tc: cuTensorMapEncodeTiled not available from the driver"); return DGMC_ERR_CUDA; }
     const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
@@ -273,27 +322,28 @@ static int lt_make_map(CUtensorMap* map, const void* base, long long rows, long 
 static int lt_bn(int n_out) { return n_out <= 64 ? 64 : 128; }
 static int lt_round(int v, int m) { return (v + m - 1) / m * m; }
 
-template <int BN>
-static int lt_launch(const CUtensorMap& mx, const CUtensorMap& mh, const CUtensorMap& ml, const float* bias,
-                     int relu, float* y, long long ldy, long long rows, int n_out, int k_blocks, int n_pad,
+template <int BN, int ACC>
+static int lt_launch(const CUtensorMap& mx, const CUtensorMap& mh, const CUtensorMap& ml,
+                     const CUtensorMap& my, int y_tma, const float* bias, int relu, float* y, long long ldy, long long rows, int n_out, int k_blocks, int n_pad,
                      cudaStream_t stream) {
     constexpr int STAGE = 2 * LT_A_BYTES + 2 * BN * LT_KB * 4;
-    // BN = 64: 2 stages of 48 KB -> two CTAs per SM interleave; BN = 128: 3 stages of 64 KB
-    int n_stages = BN == 64 ? 2 : 3;
-    if (n_stages > k_blocks) n_stages = k_blocks;
-    const size_t smem = (size_t)n_stages * STAGE + (3 * LT_MAX_STAGES + 2) * 8 + 1024;
-    static size_t configured = 0;
-    if (smem > configured) {
-        if (cudaFuncSetAttribute(linear_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    // the full ring always (>= 192 KB): one CTA per SM, which owns all 512 TMEM columns
+    const size_t smem = (size_t)lt_stages(BN) * STAGE + 4 * LT_OUT_BYTES + (3 * LT_MAX_STAGES + 6) * 8 + 1024;
+    static bool configured = false;
+    if (!configured) {
+        if (cudaFuncSetAttribute(linear_tc_kernel<BN, ACC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)smem) != cudaSuccess) {
             set_error("linear_tc: cannot set %zu bytes of dynamic shared memory", smem);
             return DGMC_ERR_CUDA;
         }
-        configured = smem;
+        configured = true;
     }
-    dim3 grid(n_pad / BN, (unsigned)((rows + LT_BM - 1) / LT_BM));
-    linear_tc_kernel<BN><<<grid, LT_THREADS, smem, stream>>>(mx, mh, ml, bias, relu, y, ldy, rows, n_out,
-                                                            k_blocks, n_stages);
+    const int n_tiles_n = n_pad / BN;
+    const long long tiles = (long long)n_tiles_n * ((rows + LT_BM - 1) / LT_BM);
+    if (tiles > 0x7fffffffLL) { set_error("linear_tc: too many tiles"); return DGMC_ERR_UNSUPPORTED; }
+    const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
+    linear_tc_kernel<BN, ACC><<<grid, LT_THREADS, smem, stream>>>(mx, mh, ml, my, y_tma, bias, relu, y, ldy, rows,
+                                                            n_out, k_blocks, n_tiles_n, (int)tiles);
     return DGMC_OK;
 }
 
@@ -303,8 +353,8 @@ static int lt_launch(const CUtensorMap& mx, const CUtensorMap& mh, const CUtenso
 using namespace dgmc;
 
 extern "C" int dgmc_linear_tc_supported(int64_t rows, int n_out, int k_in, int64_t ldx, const float* x) {
-    // TMA: 16-byte aligned base and pitch; grid.y limit
-    return rows >= 1 && rows <= (int64_t)65535 * tc::LT_BM && n_out >= 1 && k_in >= 1 && ldx >= k_in &&
+    // TMA: 16-byte aligned base and pitch; tile count fits an int
+    return rows >= 1 && rows <= (int64_t)1 << 30 && n_out >= 1 && n_out <= 65536 && k_in >= 1 && ldx >= k_in &&
            ldx % 4 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0;
 }
 
@@ -350,10 +400,18 @@ extern "C" int dgmc_linear_tc(const float* x, int64_t ldx, const void* split_wei
     if (int e = tc::lt_make_map(&mx, x, rows, k_in, ldx, tc::LT_BM)) return e;
     if (int e = tc::lt_make_map(&mh, hi, n_pad, k_pad, k_pad, bn)) return e;
     if (int e = tc::lt_make_map(&ml, lo, n_pad, k_pad, k_pad, bn)) return e;
+    // y through TMA stores when its base and pitch are 16-byte aligned, else plain stores
+    const int y_tma = (ldy % 4 == 0) && ((reinterpret_cast<uintptr_t>(y) & 15) == 0);
+    CUtensorMap my;
+    if (y_tma) { if (int e = tc::lt_make_map(&my, y, rows, n_out, ldy, 32)) return e; }
+    else my = mx;
     const int k_blocks = k_pad / tc::LT_KB;
     int e;
-    if (bn == 64) e = tc::lt_launch<64>(mx, mh, ml, bias, relu, y, ldy, rows, n_out, k_blocks, n_pad, stream);
-    else          e = tc::lt_launch<128>(mx, mh, ml, bias, relu, y, ldy, rows, n_out, k_blocks, n_pad, stream);
+    const bool short_k = k_blocks <= 4;
+#define DGMC_LT_ARGS mx, mh, ml, my, y_tma, bias, relu, y, ldy, rows, n_out, k_blocks, n_pad, stream
+    if (bn == 64) e = short_k ? tc::lt_launch<64, 1>(DGMC_LT_ARGS) : tc::lt_launch<64, 2>(DGMC_LT_ARGS);
+    else          e = short_k ? tc::lt_launch<128, 1>(DGMC_LT_ARGS) : tc::lt_launch<128, 2>(DGMC_LT_ARGS);
+#undef DGMC_LT_ARGS
     if (e) return e;
     return check_launch("linear_tc");
 }
