@@ -348,7 +348,7 @@ def diff_mlp(s_hat, ps, pt, w2, b2, cand):
 # --------------------------------------------------------------------------------------------
 # per-node linear map with a split-K weight gradient
 # --------------------------------------------------------------------------------------------
-WGRAD_TENSOR_CORE = False
+WGRAD_TENSOR_CORE = True
 
 
 class WGradGroup(object):
@@ -480,9 +480,10 @@ class _NodeLinear(torch.autograd.Function):
             return dx, dw, db, None, None, None
         m, n = n_out, k_in
         grp = ctx.group
-        # fp32 FFMA split-K kernel by default; WGRAD_TENSOR_CORE switches to the tcgen05 3xTF32
-        # kernel (correct, but staging-bound and 2x slower at these skinny shapes: DESIGN.md §8)
-        tc = WGRAD_TENSOR_CORE and bool(query('dgmc_wgrad_tc_supported', m, n))
+        # tcgen05 3xTF32 kernel on TMA-loaded MN-major tiles when the operands meet TMA's alignment
+        # rules (WGRAD_TENSOR_CORE), else the fp32 FFMA split-K kernel
+        tc = WGRAD_TENSOR_CORE and bool(query('dgmc_wgrad_tc_supported', m, n, g.stride(0), x.stride(0),
+                                              g.data_ptr(), x.data_ptr()))
         fn_splits = 'dgmc_wgrad_tc_splits' if tc else 'dgmc_wgrad_splits'
         fn_partial = 'dgmc_wgrad_tc_partial' if tc else 'dgmc_wgrad_partial'
         calls, slot = (1, 0) if grp is None else (grp.calls, ctx.slot)

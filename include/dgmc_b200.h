@@ -199,10 +199,10 @@ int dgmc_wgrad(const float* g, int64_t ldg, const float* x, int64_t ldx, int64_t
                float* dw, float* db, void* workspace, size_t workspace_bytes, dgmc_stream_t stream);
 
 /* Tensor-core variant of dgmc_wgrad_partial (same partial layout, same dgmc_wgrad_reduce): tcgen05
- * kind::tf32 with every operand split into hi + lo and three MMAs per product (hi*hi + hi*lo + lo*hi,
- * fp32 TMEM accumulator) — fp32-level accuracy (~2^-21 relative), used for the backward pass only.
- * m <= 128 output channels (dgmc_wgrad_tc_supported). */
-int dgmc_wgrad_tc_supported(int m, int n);
+ * kind::tf32 on TMA-loaded MN-major tiles, every operand split into hi + lo (rounded to tf32) and
+ * accumulated as hi*hi + hi*lo + lo*hi in fp32 TMEM accumulators — fp32-level accuracy.
+ * m <= 128 output channels; g and x need 16-byte aligned bases and pitches (dgmc_wgrad_tc_supported). */
+int dgmc_wgrad_tc_supported(int m, int n, int64_t ldg, int64_t ldx, const float* g, const float* x);
 int dgmc_wgrad_tc_splits(int64_t k, int m, int n);
 int dgmc_wgrad_tc_partial(const float* g, int64_t ldg, const float* x, int64_t ldx, int64_t k, int m, int n,
                           float* partial, float* partial_b, dgmc_stream_t stream);
