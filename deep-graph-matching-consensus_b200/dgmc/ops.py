@@ -423,6 +423,27 @@ def _linear_tc(x, split, bias, relu, n_out, k_in):
     return y
 
 
+def _wgrad_tc_chunked(a, b):
+    """dw[i, j] = sum_k a[k, i] b[k, j] on dgmc_wgrad_tc_partial, 128 columns of `a` per call
+    (the kernel's limit on the operand that becomes the UMMA N dimension).  None if TMA cannot read
+    the operands (alignment)."""
+    k, m, n = a.size(0), a.size(1), b.size(1)
+    if a.stride(1) != 1 or b.stride(1) != 1:
+        return None
+    if not query('dgmc_wgrad_tc_supported', min(m, 128), n, a.stride(0), b.stride(0), a.data_ptr(),
+                 b.data_ptr()):
+        return None
+    dw = torch.empty(m, n, dtype=torch.float32, device=a.device)
+    splits = query('dgmc_wgrad_tc_splits', k, min(m, 128), n)
+    partial = torch.empty(splits, min(m, 128) * n, dtype=torch.float32, device=a.device)
+    for c0 in range(0, m, 128):
+        mc = min(128, m - c0)
+        call('dgmc_wgrad_tc_partial', RowStrided(a[:, c0:c0 + mc]), a.stride(0), RowStrided(b), b.stride(0),
+             k, mc, n, partial, None, stream_ptr())
+        call('dgmc_wgrad_reduce', partial, None, splits, mc, n, dw[c0:c0 + mc], None, stream_ptr())
+    return dw
+
+
 class _NodeLinear(torch.autograd.Function):
     """kn = False: weight [out, in] (torch Linear); kn = True: weight [in, out] (SplineConv)."""
     @staticmethod
@@ -472,9 +493,14 @@ class _NodeLinear(torch.autograd.Function):
         if not (want_w or want_b):
             return dx, None, None, None, None, None
         if kn or weight.numel() > 64 * 1024 or k < 2048:
-            # large output or few rows: an ordinary GEMM, left to the library
+            # not a "tiny output, long reduction" shape: no grouping across consensus steps; the
+            # tensor-core split-K kernel in chunks of 128 output channels when TMA can read the
+            # operands, else an ordinary library GEMM
             if want_w:
-                dw = x.t() @ g if kn else g.t() @ x
+                a, b = (x, g) if kn else (g, x)          # dw[i, j] = sum_k a[k, i] b[k, j]
+                dw = _wgrad_tc_chunked(a, b) if (WGRAD_TENSOR_CORE and k >= 2048) else None
+                if dw is None:
+                    dw = a.t() @ b
             if want_b:
                 db = g.sum(0)
             return dx, dw, db, None, None, None

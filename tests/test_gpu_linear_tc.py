@@ -83,12 +83,14 @@ def test_linear_tc_rejects_misaligned():
 
 @pytest.mark.parametrize('kn', [False, True])
 @pytest.mark.parametrize('relu', [False, True])
-def test_node_linear_autograd(kn, relu):
+@pytest.mark.parametrize('rows,n_in,n_out', [(5000, 96, 72),      # small weight: grouped split-K path
+                                             (3000, 300, 260),    # > 64K weights: chunks of 128 channels
+                                             (600, 40, 24)])      # few rows: library weight gradient
+def test_node_linear_autograd(kn, relu, rows, n_in, n_out):
     """ops.node_linear (forward + input gradient on the tensor-core kernel, weight gradient on the
-    split-K kernel or the library) against fp64 autograd, both weight layouts."""
+    tensor-core split-K kernel or the library) against fp64 autograd, both weight layouts."""
     from dgmc import ops
     g = torch.Generator().manual_seed(11)
-    rows, n_in, n_out = 5000, 96, 72
     x = torch.randn(rows, n_in, generator=g).to(DEV).requires_grad_()
     w = (torch.randn(n_in, n_out, generator=g) * 0.1 if kn else torch.randn(n_out, n_in, generator=g) * 0.1).to(DEV).requires_grad_()
     b = torch.randn(n_out, generator=g).to(DEV).requires_grad_()
