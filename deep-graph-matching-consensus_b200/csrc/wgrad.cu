@@ -7,7 +7,9 @@
 // each CTA streams its K slice through shared memory (128-bit loads), keeps a 64 x 64 tile in
 // registers (8 x 4 per thread, fp32 FFMA), writes its partial tile to the caller's workspace, and a
 // second kernel adds the partials in split order (deterministic; no atomics).
-// FP32 throughout: the parity budget (1e-5 relative on S_L after 10 steps) rules out TF32.
+// FP32 FFMA throughout.  Since the tensor-core kernel (wgrad_tc.cu: same partial layout, same
+// reduction) this partial kernel only serves operands TMA cannot read (base or pitch not 16-byte
+// aligned); dgmc_wgrad_reduce below is shared by both.
 #include "common.cuh"
 #include "../../include/dgmc_b200.h"
 

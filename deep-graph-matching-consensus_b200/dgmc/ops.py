@@ -1,8 +1,9 @@
 """Host-side wrappers (torch.autograd.Function) around the libdgmc_b200 kernels.
 
 PyTorch provides device memory, the current stream and the autograd tape; every numeric step
-below runs in a hand-written sm_100a kernel reached through the C ABI (`native.call`).  Plain
-per-node GEMMs (`[N, c_in] x [c_in, c_out]`) are left to cuBLAS via torch.matmul in the modules.
+below runs in a hand-written sm_100a kernel reached through the C ABI (`native.call`), including
+the per-node GEMMs (`node_linear`: tcgen05 3xTF32); the library GEMM is only the route for
+operands TMA cannot address (rows or bases not 16-byte aligned) and for tiny row counts.
 """
 import torch
 

@@ -1,24 +1,40 @@
-"""Micro-benchmark: fp32 FFMA split-K weight gradient (wgrad.cu) against the tcgen05 3xTF32 kernel
-(wgrad_tc.cu) at the DBP15K psi_2 shape (K = 39,000 nodes, 64 x 192 output).  python profiles/wgrad_microbench.py"""
-import sys, torch
-import os; sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 'deep-graph-matching-consensus_b200'))
-from dgmc import ops, native
-g = torch.randn(39000, 64, device='cuda'); x = torch.randn(39000, 192, device='cuda')
-def run(tc):
-    fs, fp = ('dgmc_wgrad_tc_splits', 'dgmc_wgrad_tc_partial') if tc else ('dgmc_wgrad_splits', 'dgmc_wgrad_partial')
-    sp = native.query(fs, 39000, 64, 192)
-    part = torch.empty(sp, 64 * 192, device='cuda'); pb = torch.empty(sp, 64, device='cuda')
-    dw = torch.empty(64, 192, device='cuda'); db = torch.empty(64, device='cuda')
-    def once():
-        native.call(fp, g, 64, x, 192, 39000, 64, 192, part, pb, native.stream_ptr())
-        native.call('dgmc_wgrad_reduce', part, pb, sp, 64, 192, dw, db, native.stream_ptr())
-    for _ in range(3): once()
-    torch.cuda.synchronize()
-    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    a.record()
-    for _ in range(50): once()
-    b.record(); torch.cuda.synchronize()
-    ref = g.double().t() @ x.double()
-    return a.elapsed_time(b) / 50 * 1e3, (dw.double() - ref).abs().max().item() / ref.abs().max().item(), sp
-for tc in (False, True):
-    print('tensor_core=%s: %.1f us per wgrad (partial+reduce), max rel err %.2e, splits %d' % ((tc,) + run(tc)))
+"""Micro-benchmark: tcgen05 3xTF32 weight gradient (wgrad_tc.cu) against the fp32 FFMA split-K kernel
+(wgrad.cu): error against fp64 and device time per launch inside a replayed CUDA graph.
+python profiles/wgrad_microbench.py"""
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+                                'deep-graph-matching-consensus_b200'))
+from dgmc.native import call, query, stream_ptr, RowStrided
+dev = 'cuda'
+torch.manual_seed(0)
+def run(kind, g, x, want_b=True):
+    k, m = g.shape; n = x.shape[1]
+    splits = query('dgmc_wgrad_tc_splits' if kind == 'tc' else 'dgmc_wgrad_splits', k, m, n)
+    partial = torch.empty(splits, m * n, device=dev); pb = torch.empty(splits, m, device=dev)
+    dw = torch.empty(m, n, device=dev); db = torch.empty(m, device=dev)
+    def fn():
+        call('dgmc_wgrad_tc_partial' if kind == 'tc' else 'dgmc_wgrad_partial', g, g.stride(0), RowStrided(x), x.stride(0), k, m, n, partial, pb, stream_ptr())
+    def red():
+        call('dgmc_wgrad_reduce', partial, pb, splits, m, n, dw, db, stream_ptr())
+    fn(); red(); torch.cuda.synchronize()
+    def t(f, reps=20):
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr):
+            for _ in range(reps): f()
+        gr.replay(); torch.cuda.synchronize()
+        a, c = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); gr.replay(); c.record(); torch.cuda.synchronize()
+        return a.elapsed_time(c) / reps * 1e3
+    return dw, db, t(fn), t(red), splits
+for k, m, n in [(3000, 8, 24), (38960, 64, 192), (38960, 64, 256), (38960, 64, 64), (100000, 128, 300), (5000, 36, 72)]:
+    g = torch.randn(k, m, device=dev); x = torch.randn(k, n, device=dev)
+    ref_w = g.double().t() @ x.double(); ref_b = g.double().sum(0)
+    for kind in ('ffma', 'tc'):
+        dw, db, tp, tr, splits = run(kind, g, x)
+        ew = (dw.double() - ref_w).abs().max().item() / ref_w.abs().max().item()
+        eb = (db.double() - ref_b).abs().max().item() / ref_b.abs().max().item()
+        print('k %6d m %3d n %3d %-4s splits %4d: err dw %.2e db %.2e | partial %.1f us reduce %.1f us' % (k, m, n, kind, splits, ew, eb, tp, tr), flush=True)
