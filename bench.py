@@ -206,12 +206,46 @@ def timed(fn, iters, flush=None):
     return total / iters
 
 
+def timed_graph(fn, iters, flush):
+    """Like timed(), for calls whose host side (tensor-map encoding, autograd) takes longer than the
+    kernels: [flush, fn] and [flush] are captured as CUDA graphs and the difference of their replay
+    times is the device time of fn with a cold L2."""
+    def capture(body):
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            body()
+        return g
+
+    def replay_ms(g):
+        g.replay()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(iters):
+            g.replay()
+        b.record()
+        b.synchronize()
+        return a.elapsed_time(b) / iters
+    fn()
+    torch.cuda.synchronize()
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        g1 = capture(lambda: (flush.zero_(), fn()))
+        g0 = capture(lambda: flush.zero_())
+        t1, t0 = replay_ms(g1), replay_ms(g0)
+    torch.cuda.current_stream().wait_stream(side)
+    return max(t1 - t0, 1e-4)
+
+
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the `ncu --set full` captures under
 # profiles/ (DBP15K shape only; None where the captured launch is not the one timed here)
 NCU_TRAFFIC_DBP15K = {
     'K1': 19.98e6 + 47.37e6,  # topk_tc_kernel + topk_merge_kernel (r1f/r1j captures; the two cast
                               # kernels, 40 MB fp32 in / 20 MB bf16 out, were not captured)
     'K6': 13.08e6,            # diff_mlp_fwd_kernel<16,1> (r1f capture)
+    'G1': 30.04e6,            # linear_tc_kernel<64,2>, 38,960 x 192 -> 64 (r1n capture: X once; y stays in L2)
+    'G2': 39.96e6,            # wgrad_tc_kernel<64> (r1n capture: G and X once; the reduce kernel not captured)
 }
 
 
@@ -251,8 +285,8 @@ def kernel_rooflines(w, model, e_t, peaks, step_ms, iters=5):
 
     dbp15k = (n_s, n_t, C, R) == (19388, 19572, 256, 64)
 
-    def add(name, fn, calls, work, bound, basis=''):
-        ms = timed(fn, iters, flush)
+    def add(name, fn, calls, work, bound, basis='', graphed=False):
+        ms = timed_graph(fn, iters, flush) if graphed else timed(fn, iters, flush)
         traffic = NCU_TRAFFIC_DBP15K.get(name[:2]) if dbp15k else None
         achieved = work / (ms * 1e-3) / (1e12 if bound == 'tensor' else 1e9)
         peak = tf if bound == 'tensor' else hbm
@@ -280,6 +314,35 @@ def kernel_rooflines(w, model, e_t, peaks, step_ms, iters=5):
         wk, b = pick(n_t * 4 * R, 4 * R * (n_s + n_t) + 12 * n_s * k_eff,
                      4 * R * n_s * (1 + k_eff) + 12 * n_s * k_eff)
         add('K6 diff_mlp fwd', lambda: ops.diff_mlp(S, p_s, p_t, w2, b2, cand), T, wk, 'hbm', b)
+        # psi_2 RelConv GEMM on the merged pair: [N_s + N_t, 3R] -> R, bias + ReLU (tcgen05 3xTF32).
+        # Bound by HBM, not by the tensor pipe: 3 x 2*N*3R*R flop is 2.9 GFLOP (2 us at peak).
+        n_m = n_s + n_t
+        cat, wl, bl = rnd(n_m, 3 * R), rnd(R, 3 * R) * 0.05, rnd(R)
+        add('G1 linear_tc (psi_2 RelConv GEMM, merged pair)',
+            lambda: ops.node_linear(cat, wl, bl, relu=True), (L + 1) * T, 4 * n_m * (3 * R + R), 'hbm', 'min',
+            graphed=True)
+    gy = rnd(n_m, R)
+    cat.requires_grad_(False)
+    wl.requires_grad_(True)
+
+    def wgrad_once():
+        wl.grad = None
+        y = ops.node_linear(cat, wl)
+        y.backward(gy)
+    with torch.enable_grad():
+        # weight gradient dW [R, 3R] = G^T X over N nodes (split-K tcgen05 + reduce); the timed call
+        # includes the forward GEMM above, which is subtracted
+        t_pair = timed_graph(wgrad_once, iters, flush)
+    with torch.no_grad():
+        t_fwd = timed_graph(lambda: ops.node_linear(cat, wl), iters, flush)
+    ms = max(t_pair - t_fwd, 1e-4)
+    work = 4 * n_m * (3 * R + R)
+    rows.append({'kernel': 'G2 wgrad_tc + reduce (psi_2 RelConv weight gradient)', 'bound': 'hbm',
+                 'achieved': round(work / (ms * 1e-3) / 1e9, 2), 'peak': hbm, 'unit': 'GB/s',
+                 'frac': round(work / (ms * 1e-3) / 1e9 / hbm, 4),
+                 'traffic': NCU_TRAFFIC_DBP15K.get('G2') if dbp15k else None, 'work_basis': 'min',
+                 'logical_gbs': None, 'ms_per_launch': round(ms, 4), 'launches_per_step': (L + 1) * T,
+                 'share_of_step': round(ms * (L + 1) * T / step_ms, 4) if step_ms else None})
     return rows
 
 
