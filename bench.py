@@ -174,6 +174,8 @@ def build_model(w, device, sharded=False):
                    dropout=0.0)
     cls = RowShardedDGMC if sharded else DGMC
     model = cls(psi_1, psi_2, num_steps=w['num_steps'], k=w['k'], detach=True).to(device)
+    if sharded and os.environ.get('DGMC_SHARD_PSI'):      # study switch: 0 / 1 instead of 'auto'
+        model.shard_psi = bool(int(os.environ['DGMC_SHARD_PSI']))
     model.train()
     return model
 

@@ -170,11 +170,16 @@ class RowShardedDGMC(DGMC):
     `.__idx__`, `.__val__` and `.__rows__ = (lo, hi)`; `loss` / `acc` / `hits_at_k` take the GLOBAL
     ground truth `y` and reduce over all ranks."""
 
-    def __init__(self, psi_1, psi_2, num_steps, k, detach=False, group=None, shard_psi=True):
+    # node-sharding psi_2 adds 2 (L + 1) collectives per consensus step; below this many nodes
+    # (source + target) they cost more than the replicated psi_2 they save
+    SHARD_PSI_MIN_NODES = 150000
+
+    def __init__(self, psi_1, psi_2, num_steps, k, detach=False, group=None, shard_psi='auto'):
         super().__init__(psi_1, psi_2, num_steps, k=k, detach=detach)
         assert k >= 1, 'row sharding applies to the sparse variant (k >= 1)'
         self.group = group
-        self.shard_psi = shard_psi  # node-shard psi_2 (RelCNN) instead of running it replicated
+        # node-shard psi_2 (RelCNN) instead of running it replicated: True / False / 'auto' (by size)
+        self.shard_psi = shard_psi
 
     def _world(self):
         return dist.get_rank(self.group), dist.get_world_size(self.group)
@@ -197,7 +202,8 @@ class RowShardedDGMC(DGMC):
                                    edge_attr_s, edge_attr_t, N_s, N_t)
         from .rel import RelCNN
         sp = None
-        if self.shard_psi and world > 1 and merged is not None and isinstance(self.psi_2, RelCNN):
+        shard_psi = (N_s + N_t >= self.SHARD_PSI_MIN_NODES) if self.shard_psi == 'auto' else self.shard_psi
+        if shard_psi and world > 1 and merged is not None and isinstance(self.psi_2, RelCNN):
             sp = ShardedPair.of(edge_index_s, edge_index_t, N_s, N_t, rank, world)
 
         h_loc = h_s[lo:hi]
