@@ -183,7 +183,38 @@ __global__ void __launch_bounds__(256) gather_dot_generic_kernel(
 
 }  // namespace dgmc
 
+namespace dgmc {
+// out[i, :] = y[i, :] > 0 ? g[i, :] : 0 on row-strided operands, one float4 per thread
+__global__ void __launch_bounds__(256) relu_bwd_kernel(const float* __restrict__ g, long long ldg,
+                                                       const float* __restrict__ y, long long ldy,
+                                                       float* __restrict__ out, long long ldo,
+                                                       long long rows, int c4) {
+    const long long total = rows * c4;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += stride) {
+        const long long i = t / c4;
+        const int q = (int)(t % c4) * 4;
+        const float4 gv = ldg4(g + i * ldg + q), yv = ldg4(y + i * ldy + q);
+        *reinterpret_cast<float4*>(out + i * ldo + q) =
+            make_float4(yv.x > 0.f ? gv.x : 0.f, yv.y > 0.f ? gv.y : 0.f, yv.z > 0.f ? gv.z : 0.f,
+                        yv.w > 0.f ? gv.w : 0.f);
+    }
+}
+}  // namespace dgmc
+
 using namespace dgmc;
+
+extern "C" int dgmc_relu_bwd(const float* g, int64_t ldg, const float* y, int64_t ldy, float* out,
+                             int64_t ldo, int64_t rows, int c, dgmc_stream_t stream) {
+    if (rows == 0) return DGMC_OK;
+    DGMC_REQUIRE(g && y && out && rows > 0 && c >= 4 && c % 4 == 0 && ldg % 4 == 0 && ldy % 4 == 0 &&
+                     ldo % 4 == 0 && ldg >= c && ldy >= c && ldo >= c &&
+                     ((reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(y) |
+                       reinterpret_cast<uintptr_t>(out)) & 15) == 0,
+                 "relu_bwd: needs c %% 4 == 0 and 16-byte aligned rows (c=%d)", c);
+    relu_bwd_kernel<<<wave_grid(rows * (c / 4), 256, 8), 256, 0, stream>>>(g, ldg, y, ldy, out, ldo, rows, c / 4);
+    return check_launch("relu_bwd");
+}
 
 extern "C" int dgmc_softmax_k_fwd(const float* x, float* y, int64_t rows, int k,
                                   dgmc_stream_t stream) {

@@ -25,14 +25,19 @@ class RelConv(torch.nn.Module):
         for lin in (self.lin1, self.lin2, self.root):
             lin.reset_parameters()
 
-    def forward(self, x, edge_index, relu=False):
+    def forward(self, x, edge_index, relu=False, out=None, passthrough=False):
         """relu=True additionally applies the ReLU that RelCNN puts after every conv (rel.py:84-85),
-        fused into the GEMM epilogue."""
+        fused into the GEMM epilogue.  out: write the result into this column block of a layer
+        buffer; passthrough: also return x as handed through the aggregation (ops._RelAggregatePass)."""
         graph = ops.GraphCSR.of(edge_index, x.size(0))
-        stacked = ops.rel_aggregate(x, graph)  # [N, 3 C_in] = [x | mean_in | mean_out]
+        if passthrough:
+            stacked, alias = ops.rel_aggregate_pass(x, graph)
+        else:
+            stacked = ops.rel_aggregate(x, graph)  # [N, 3 C_in] = [x | mean_in | mean_out]
         weight = ops.region_cached(('relconv', id(self)), lambda: torch.cat(
             [self.root.weight, self.lin1.weight, self.lin2.weight], dim=1))
-        return ops.node_linear(stacked, weight, self.root.bias, relu=relu, key=('relconv', id(self)))
+        y = ops.node_linear(stacked, weight, self.root.bias, relu=relu, key=('relconv', id(self)), out=out)
+        return (y, alias) if passthrough else y
 
     def __repr__(self):
         return '{}({}, {})'.format(type(self).__name__, self.in_channels, self.out_channels)
@@ -65,7 +70,29 @@ class RelCNN(torch.nn.Module):
         if self.lin:
             self.final.reset_parameters()
 
+    def _direct_cat(self, x):
+        """The layers can write straight into the concatenated [N, in + L*out] buffer: no batch norm
+        or dropout between a layer and the concatenation, float4-aligned column blocks."""
+        return (self.cat and not self.batch_norm and not (self.training and self.dropout > 0)
+                and x.is_cuda and x.dtype == torch.float32 and x.dim() == 2
+                and self.in_channels % 4 == 0 and self.convs[0].out_channels % 4 == 0)
+
+    def _forward_direct(self, x, edge_index):
+        c_in, c_out = self.in_channels, self.convs[0].out_channels
+        buf = torch.empty(x.size(0), c_in + self.num_layers * c_out, dtype=torch.float32, device=x.device)
+        cur, parts, off = ops.copy_into(x, buf, 0), [], c_in
+        for conv in self.convs:
+            cur, alias = conv(cur, edge_index, relu=True, out=buf[:, off:off + c_out], passthrough=True)
+            parts.append(alias)
+            off += c_out
+        parts.append(cur)
+        out = ops.join_slices(buf, self.lin, *parts)
+        return ops.node_linear(out, self.final.weight, self.final.bias, key=('final', id(self))) \
+            if self.lin else out
+
     def forward(self, x, edge_index, *args):
+        if self._direct_cat(x):
+            return self._forward_direct(x, edge_index)
         feats = [x]
         for conv, norm in zip(self.convs, self.batch_norms):
             h = conv(feats[-1], edge_index, relu=True)

@@ -417,10 +417,11 @@ def _split_weight(weight, transposed, holder=None, slot=None):
     return ws
 
 
-def _linear_tc(x, split, bias, relu, n_out, k_in):
-    y = torch.empty(x.size(0), n_out, dtype=torch.float32, device=x.device)
-    call('dgmc_linear_tc', RowStrided(x), x.stride(0), split, bias, int(relu), y, n_out, x.size(0),
-         n_out, k_in, stream_ptr())
+def _linear_tc(x, split, bias, relu, n_out, k_in, out=None):
+    """`out`: optional [rows, n_out] row-strided destination (e.g. a column block of a wider buffer)."""
+    y = torch.empty(x.size(0), n_out, dtype=torch.float32, device=x.device) if out is None else out
+    call('dgmc_linear_tc', RowStrided(x), x.stride(0), split, bias, int(relu), RowStrided(y), y.stride(0),
+         x.size(0), n_out, k_in, stream_ptr())
     return y
 
 
@@ -448,16 +449,19 @@ def _wgrad_tc_chunked(a, b):
 class _NodeLinear(torch.autograd.Function):
     """kn = False: weight [out, in] (torch Linear); kn = True: weight [in, out] (SplineConv)."""
     @staticmethod
-    def forward(ctx, x, weight, bias, relu, group, kn):
+    def forward(ctx, x, weight, bias, relu, group, kn, out):
         k_in, n_out = (weight.size(0), weight.size(1)) if kn else (weight.size(1), weight.size(0))
         if _linear_tc_ok(x, n_out, k_in):
-            y = _linear_tc(x, _split_weight(weight, kn, group, 'split_fwd'), bias, relu, n_out, k_in)
+            y = _linear_tc(x, _split_weight(weight, kn, group, 'split_fwd'), bias, relu, n_out, k_in, out)
         else:
             w_kn = weight if kn else weight.t()
             if relu:  # bias + ReLU in the library GEMM's epilogue
                 y = torch._addmm_activation(bias, x, w_kn, use_gelu=False)
             else:
                 y = torch.addmm(bias, x, w_kn) if bias is not None else x @ w_kn
+            if out is not None:
+                out.copy_(y)
+                y = out
         if relu:
             ctx.save_for_backward(x, weight, y)
         else:
@@ -472,7 +476,14 @@ class _NodeLinear(torch.autograd.Function):
     def backward(ctx, g):
         if ctx.relu:
             x, weight, y = ctx.saved_tensors
-            g = torch.ops.aten.threshold_backward(g, y, 0)  # g * (y > 0) in one kernel
+            if g.dim() == 2 and g.stride(1) == 1 and y.stride(1) == 1 and _vec_ok(g) and _vec_ok(y) \
+                    and g.dtype == torch.float32:
+                gm = torch.empty(g.size(0), g.size(1), dtype=torch.float32, device=g.device)
+                call('dgmc_relu_bwd', RowStrided(g), g.stride(0), RowStrided(y), y.stride(0), gm, gm.stride(0),
+                     g.size(0), g.size(1), stream_ptr())   # g * (y > 0), row-strided operands
+                g = gm
+            else:
+                g = torch.ops.aten.threshold_backward(g, y, 0)
         else:
             x, weight = ctx.saved_tensors
         g = _f32(g)
@@ -492,7 +503,7 @@ class _NodeLinear(torch.autograd.Function):
         want_w = ctx.needs_input_grad[1]
         want_b = ctx.has_bias and ctx.needs_input_grad[2]
         if not (want_w or want_b):
-            return dx, None, None, None, None, None
+            return dx, None, None, None, None, None, None
         if kn or weight.numel() > 64 * 1024 or k < 2048:
             # not a "tiny output, long reduction" shape: no grouping across consensus steps; the
             # tensor-core split-K kernel in chunks of 128 output channels when TMA can read the
@@ -504,7 +515,7 @@ class _NodeLinear(torch.autograd.Function):
                     dw = a.t() @ b
             if want_b:
                 db = g.sum(0)
-            return dx, dw, db, None, None, None
+            return dx, dw, db, None, None, None, None
         m, n = n_out, k_in
         grp = ctx.group
         # tcgen05 3xTF32 kernel on TMA-loaded MN-major tiles when the operands meet TMA's alignment
@@ -535,21 +546,24 @@ class _NodeLinear(torch.autograd.Function):
             holder.partial = holder.partial_b = None
             holder.split_fwd = holder.split_bwd = None
             holder.done = 0  # a second backward over a retained graph starts afresh
-        return dx, dw, db, None, None, None
+        return dx, dw, db, None, None, None, None
 
 
-def node_linear(x, weight, bias=None, relu=False, key=None, kn=False):
+def node_linear(x, weight, bias=None, relu=False, key=None, kn=False, out=None):
     """relu?(x [nodes, in] @ W + bias) with W = weight[out, in]^T (kn=False) or weight[in, out]
     (kn=True).  Forward and input gradient run on the tensor-core kernel dgmc_linear_tc (3xTF32,
     bias and ReLU in its epilogue) whenever x meets TMA's alignment rules, else on the library GEMM;
     the weight / bias gradient (a reduction over all nodes with a tiny output) runs on the split-K
-    kernel dgmc_wgrad when the output is small, else stays with the library."""
+    kernel dgmc_wgrad when the output is small, else stays with the library.  `out`: write the
+    result into this row-strided [nodes, out] view (a column block of a layer buffer) instead of a
+    fresh tensor."""
     if x.is_cuda and x.dtype == torch.float32 and x.dim() == 2 and x.stride(1) == 1 \
             and weight.dtype == torch.float32 and (bias is not None or not relu):
         group = None
         if key is not None and _DEFER[0] is not None and torch.is_grad_enabled():
             group = _DEFER[0].setdefault((key, x.size(0), tuple(weight.shape)), WGradGroup())
-        return _NodeLinear.apply(x, weight, bias, relu, group, kn)
+        return _NodeLinear.apply(x, weight, bias, relu, group, kn, out)
+    assert out is None, 'node_linear(out=...) is a CUDA fp32 feature'
     y = torch.addmm(bias, x, weight) if (kn and bias is not None) else (
         x @ weight if kn else torch.nn.functional.linear(x, weight, bias))
     return torch.relu(y) if relu else y
@@ -581,6 +595,96 @@ class _RelAggregate(torch.autograd.Function):
         dx = segment_gather(g.view(3 * rel.n_out, c), rel.n_in, rel.b_src, ptr=rel.b_ptr, w=rel.b_w,
                             seg_of=rel.b_seg)
         return dx, None
+
+
+def _rows_f32(t):
+    """fp32 2-D tensor with unit column stride (row pitch may exceed the width)."""
+    if t.dtype != torch.float32:
+        raise native.DgmcNativeError('dgmc (B200): kernels compute in fp32, got %s' % t.dtype)
+    return t if (t.dim() == 2 and t.stride(1) == 1) else t.contiguous()
+
+
+class _RelAggregatePass(torch.autograd.Function):
+    """_RelAggregate that also hands its input through as a second output.  A layer input that
+    feeds both the aggregation and the final concatenation then has ONE consumer in the autograd
+    graph, and the backward adds the two gradients inside the gather kernel (accumulate mode, in
+    place in the concatenation's gradient block) instead of in a separate add kernel."""
+    @staticmethod
+    def forward(ctx, x, rel):
+        x = _rows_f32(x)
+        c = x.size(1)
+        cat = torch.empty(rel.n_out, 3 * c, dtype=torch.float32, device=x.device)
+        segment_gather(x, 3 * rel.n_out, rel.f_src, ptr=rel.f_ptr, w=rel.f_w,
+                       out=cat.view(3 * rel.n_out, c), seg_of=rel.f_seg)
+        ctx.rel = rel
+        return cat, x.view_as(x)
+
+    @staticmethod
+    def backward(ctx, g, g_pass):
+        if not ctx.needs_input_grad[0]:
+            return None, None
+        rel = ctx.rel
+        g = _f32(g)
+        c = g.size(1) // 3
+        g_pass = _rows_f32(g_pass)
+        if not _vec_ok(g_pass):
+            g_pass = g_pass.contiguous()
+        dx = segment_gather(g.view(3 * rel.n_out, c), rel.n_in, rel.b_src, ptr=rel.b_ptr, w=rel.b_w,
+                            seg_of=rel.b_seg, out=g_pass, accumulate=True)
+        return dx, None
+
+
+def rel_aggregate_pass(x, graph):
+    """-> (rel_aggregate(x, graph), x); see _RelAggregatePass."""
+    return _RelAggregatePass.apply(x, graph.rel)
+
+
+class _CopyInto(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, buf, offset):
+        view = buf[:, offset:offset + x.size(1)]
+        view.copy_(x)
+        return view
+
+    @staticmethod
+    def backward(ctx, g):
+        return g, None, None
+
+
+def copy_into(x, buf, offset):
+    """buf[:, offset : offset + x.size(1)] = x; returns that column block (gradient: identity)."""
+    return _CopyInto.apply(x, buf, offset)
+
+
+class _JoinSlices(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, buf, own_grad, *parts):
+        off = 0
+        for part in parts:  # the parts must already BE the column blocks of buf, in order
+            assert part.data_ptr() == buf.data_ptr() + 4 * off and part.stride(0) == buf.stride(0)
+            off += part.size(1)
+        assert off == buf.size(1)
+        ctx.widths, ctx.own_grad = [part.size(1) for part in parts], own_grad
+        return buf.view_as(buf)
+
+    @staticmethod
+    def backward(ctx, g):
+        if not ctx.own_grad or g.stride(1) != 1:
+            g = g.clone(memory_format=torch.contiguous_format)  # consumers accumulate into their block in place
+        outs, off = [], 0
+        for width in ctx.widths:
+            outs.append(g[:, off:off + width])
+            off += width
+        return (None, None) + tuple(outs)
+
+
+def join_slices(buf, own_grad, *parts):
+    """torch.cat(parts, dim=-1) when every part was written straight into its column block of `buf`
+    (node_linear(out=...), copy_into): no copy in the forward pass, column views of the gradient in
+    the backward pass.  own_grad: the gradient of the result is produced by this package's own
+    GEMM backward and may be modified in place by the consumers of the parts; otherwise it is cloned
+    first."""
+    return _JoinSlices.apply(buf, own_grad, *parts)
 
 
 def rel_aggregate(x, graph):

@@ -207,6 +207,12 @@ int dgmc_wgrad_tc_splits(int64_t k, int m, int n);
 int dgmc_wgrad_tc_partial(const float* g, int64_t ldg, const float* x, int64_t ldx, int64_t k, int m, int n,
                           float* partial, float* partial_b, dgmc_stream_t stream);
 
+/* out[i, 0:c] = y[i, 0:c] > 0 ? g[i, 0:c] : 0 on row-strided operands (column blocks of wider
+ * buffers): the ReLU backward between two RelConv layers (rel.py:84-85) when the activations live in
+ * the concatenated layer buffer.  c % 4 == 0, 16-byte aligned rows. */
+int dgmc_relu_bwd(const float* g, int64_t ldg, const float* y, int64_t ldy, float* out, int64_t ldo,
+                  int64_t rows, int c, dgmc_stream_t stream);
+
 /* ---- per-node linear map on the tensor cores ------------------------------------------------
  * y[rows, n_out] = relu?(x[rows, k_in] w[n_out, k_in]^T + bias): the GEMM inside every RelConv
  * (rel.py:27-30 after hoisting the aggregation), SplineConv (spline.py:40-47), Lin (rel.py:66 /
