@@ -209,6 +209,14 @@ class DGMC(torch.nn.Module):
             S = ops.softmax_k(S_hat)
             r_s = torch.randn((B, N_s, R_in), dtype=h_s.dtype, device=h_s.device)
             r_t = ops.transport(S, r_s.view(B * N_s, R_in), cand)
+            if merged is not None and s_mask is None and t_mask is None:
+                # one un-padded pair: psi_2 and the hoisted first MLP layer on the merged node table,
+                # which K6 reads (and whose gradient its backward writes) as one tensor
+                o = self.psi_2(torch.cat([r_s.view(B * N_s, R_in), r_t], dim=0), merged.edge_index,
+                               merged.edge_attr)
+                p = ops.node_linear(o, w1, key=('mlp0', id(self)))
+                S_hat = ops.diff_mlp_merged(S_hat, p, B * N_s, b1, w2, b2, cand)
+                continue
             p_s, p_t = consensus_nodes(r_s, r_t)
             S_hat = ops.diff_mlp(S_hat, p_s, p_t, w2, b2, cand)
         S_L = _rows(ops.softmax_k(S_hat), s_mask)
