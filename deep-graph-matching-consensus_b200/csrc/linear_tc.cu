@@ -76,7 +76,8 @@ template <int BN, int LT_ACC>
 __global__ void __launch_bounds__(LT_THREADS, 1)
 linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_whi,
                  const __grid_constant__ CUtensorMap map_wlo, const __grid_constant__ CUtensorMap map_y,
-                 int y_tma, const float* __restrict__ bias, int relu, float* __restrict__ y, long long ldy,
+                 int y_tma, const float* __restrict__ bias, long long bias_rows, int relu, float* __restrict__ y,
+                 long long ldy,
                  long long rows, int n_out, int k_blocks, int n_tiles_n, int n_tiles) {
     constexpr int B_BYTES = BN * LT_KB * 4;
     constexpr int STAGE_BYTES = 2 * LT_A_BYTES + 2 * B_BYTES;
@@ -241,7 +242,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                     if (lane == 0) mbar_arrive(&acc_empty[buf]);
                 }
                 const int c0 = n0 + cb;
-                if (bias) {
+                if (bias && row < bias_rows) {       // the bias may apply to the leading rows only
 #pragma unroll
                     for (int j = 0; j < 32; ++j) r[j] += (c0 + j < n_out) ? __ldg(bias + c0 + j) : 0.f;
                 }
@@ -324,7 +325,7 @@ static int lt_round(int v, int m) { return (v + m - 1) / m * m; }
 
 template <int BN, int ACC>
 static int lt_launch(const CUtensorMap& mx, const CUtensorMap& mh, const CUtensorMap& ml,
-                     const CUtensorMap& my, int y_tma, const float* bias, int relu, float* y, long long ldy, long long rows, int n_out, int k_blocks, int n_pad,
+                     const CUtensorMap& my, int y_tma, const float* bias, long long bias_rows, int relu, float* y, long long ldy, long long rows, int n_out, int k_blocks, int n_pad,
                      cudaStream_t stream) {
     constexpr int STAGE = 2 * LT_A_BYTES + 2 * BN * LT_KB * 4;
     // the full ring always (>= 192 KB): one CTA per SM, which owns all 512 TMEM columns
@@ -342,7 +343,7 @@ static int lt_launch(const CUtensorMap& mx, const CUtensorMap& mh, const CUtenso
     const long long tiles = (long long)n_tiles_n * ((rows + LT_BM - 1) / LT_BM);
     if (tiles > 0x7fffffffLL) { set_error("linear_tc: too many tiles"); return DGMC_ERR_UNSUPPORTED; }
     const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
-    linear_tc_kernel<BN, ACC><<<grid, LT_THREADS, smem, stream>>>(mx, mh, ml, my, y_tma, bias, relu, y, ldy, rows,
+    linear_tc_kernel<BN, ACC><<<grid, LT_THREADS, smem, stream>>>(mx, mh, ml, my, y_tma, bias, bias_rows, relu, y, ldy, rows,
                                                             n_out, k_blocks, n_tiles_n, (int)tiles);
     return DGMC_OK;
 }
@@ -383,9 +384,9 @@ extern "C" int dgmc_linear_tc_split_weight(const float* w, int64_t ldw, int tran
     return check_launch("linear_tc_split_weight");
 }
 
-extern "C" int dgmc_linear_tc(const float* x, int64_t ldx, const void* split_weight, const float* bias,
-                              int relu, float* y, int64_t ldy, int64_t rows, int n_out, int k_in,
-                              dgmc_stream_t stream) {
+static int linear_tc_impl(const float* x, int64_t ldx, const void* split_weight, const float* bias,
+                          int64_t bias_rows, int relu, float* y, int64_t ldy, int64_t rows, int n_out, int k_in,
+                          dgmc_stream_t stream) {
     DGMC_REQUIRE(x && split_weight && y && ldy >= n_out, "linear_tc: bad arguments");
     if (!dgmc_linear_tc_supported(rows, n_out, k_in, ldx, x)) {
         set_error("linear_tc: unsupported operand (rows=%lld n_out=%d k_in=%d ldx=%lld; x needs a 16-byte "
@@ -408,10 +409,22 @@ extern "C" int dgmc_linear_tc(const float* x, int64_t ldx, const void* split_wei
     const int k_blocks = k_pad / tc::LT_KB;
     int e;
     const bool short_k = k_blocks <= 4;
-#define DGMC_LT_ARGS mx, mh, ml, my, y_tma, bias, relu, y, ldy, rows, n_out, k_blocks, n_pad, stream
+#define DGMC_LT_ARGS mx, mh, ml, my, y_tma, bias, bias_rows, relu, y, ldy, rows, n_out, k_blocks, n_pad, stream
     if (bn == 64) e = short_k ? tc::lt_launch<64, 1>(DGMC_LT_ARGS) : tc::lt_launch<64, 2>(DGMC_LT_ARGS);
     else          e = short_k ? tc::lt_launch<128, 1>(DGMC_LT_ARGS) : tc::lt_launch<128, 2>(DGMC_LT_ARGS);
 #undef DGMC_LT_ARGS
     if (e) return e;
     return check_launch("linear_tc");
+}
+
+extern "C" int dgmc_linear_tc(const float* x, int64_t ldx, const void* split_weight, const float* bias, int relu,
+                              float* y, int64_t ldy, int64_t rows, int n_out, int k_in, dgmc_stream_t stream) {
+    return linear_tc_impl(x, ldx, split_weight, bias, rows, relu, y, ldy, rows, n_out, k_in, stream);
+}
+
+extern "C" int dgmc_linear_tc_rows(const float* x, int64_t ldx, const void* split_weight, const float* bias,
+                                   int64_t bias_rows, int relu, float* y, int64_t ldy, int64_t rows, int n_out,
+                                   int k_in, dgmc_stream_t stream) {
+    DGMC_REQUIRE(bias_rows >= 0 && bias_rows <= rows, "linear_tc_rows: bias_rows out of range");
+    return linear_tc_impl(x, ldx, split_weight, bias, bias_rows, relu, y, ldy, rows, n_out, k_in, stream);
 }

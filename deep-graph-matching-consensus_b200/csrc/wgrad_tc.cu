@@ -59,8 +59,8 @@ __device__ __forceinline__ uint64_t umma_desc_mn_sw128(uint32_t smem_addr, uint3
 template <int BN>   // padded output channels
 __global__ void __launch_bounds__(WT_THREADS, 1)
 wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_g,
-                long long K, int M, int N, int splits, int n_stages, float* __restrict__ partial,
-                float* __restrict__ partial_b) {
+                long long K, int M, int N, int splits, int n_stages, long long bias_rows,
+                float* __restrict__ partial, float* __restrict__ partial_b) {
     constexpr int B_BYTES = BN * WT_KB * 4;
     constexpr int STAGE_BYTES = 2 * WT_A_BYTES + 2 * B_BYTES;
     constexpr int QUADS = BN / 4;                 // 4-channel groups of G per k row
@@ -184,7 +184,9 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant
                 const uint32_t o = g_off + (uint32_t)(k * 128) +
                                    (uint32_t)((((c16 >> 1) ^ (k & 3)) << 5) | ((c16 & 1) << 4));
                 const float4 v = *reinterpret_cast<const float4*>(b_hi + o);
-                bsum.x += v.x; bsum.y += v.y; bsum.z += v.z; bsum.w += v.w;
+                if (k_begin + (long long)c * WT_KB + k < bias_rows) {   // the bias may belong to the leading rows only
+                    bsum.x += v.x; bsum.y += v.y; bsum.z += v.z; bsum.w += v.w;
+                }
                 float4 h, l;
                 wt_split4(v, h, l);
                 *reinterpret_cast<float4*>(b_hi + o) = h;
@@ -279,7 +281,7 @@ static size_t wt_smem(int bn) {
 
 template <int BN>
 static int wt_launch(const CUtensorMap& mx, const CUtensorMap& mg, long long K, int M, int N, int splits,
-                     float* partial, float* partial_b, cudaStream_t stream) {
+                     long long bias_rows, float* partial, float* partial_b, cudaStream_t stream) {
     const size_t smem = wt_smem(BN);
     static bool configured = false;
     if (!configured) {
@@ -291,7 +293,7 @@ static int wt_launch(const CUtensorMap& mx, const CUtensorMap& mg, long long K, 
         configured = true;
     }
     dim3 grid((N + WT_TN - 1) / WT_TN, splits);
-    wgrad_tc_kernel<BN><<<grid, WT_THREADS, smem, stream>>>(mx, mg, K, M, N, splits, wt_stages(BN), partial, partial_b);
+    wgrad_tc_kernel<BN><<<grid, WT_THREADS, smem, stream>>>(mx, mg, K, M, N, splits, wt_stages(BN), bias_rows, partial, partial_b);
     return DGMC_OK;
 }
 
@@ -321,8 +323,9 @@ extern "C" int dgmc_wgrad_tc_splits(int64_t k, int m, int n) {
     return wgrad_tc_splits_impl(k, n);
 }
 
-extern "C" int dgmc_wgrad_tc_partial(const float* g, int64_t ldg, const float* x, int64_t ldx, int64_t k,
-                                     int m, int n, float* partial, float* partial_b, dgmc_stream_t stream) {
+static int wgrad_tc_partial_impl(const float* g, int64_t ldg, const float* x, int64_t ldx, int64_t k, int m,
+                                 int n, int64_t bias_rows, float* partial, float* partial_b,
+                                 dgmc_stream_t stream) {
     DGMC_REQUIRE(g && x && partial && k >= 1 && k < ((int64_t)1 << 31), "wgrad_tc_partial: bad arguments");
     if (!dgmc_wgrad_tc_supported(m, n, ldg, ldx, g, x)) {
         set_error("wgrad_tc_partial: unsupported operands (m=%d of 1..%d output channels; g and x need "
@@ -334,8 +337,20 @@ extern "C" int dgmc_wgrad_tc_partial(const float* g, int64_t ldg, const float* x
     if (int e = tc::wt_make_map(&mg, g, k, m, ldg)) return e;
     const int splits = wgrad_tc_splits_impl(k, n);
     int e;
-    if (m <= 64) e = tc::wt_launch<64>(mx, mg, k, m, n, splits, partial, partial_b, stream);
-    else         e = tc::wt_launch<128>(mx, mg, k, m, n, splits, partial, partial_b, stream);
+    if (m <= 64) e = tc::wt_launch<64>(mx, mg, k, m, n, splits, bias_rows, partial, partial_b, stream);
+    else         e = tc::wt_launch<128>(mx, mg, k, m, n, splits, bias_rows, partial, partial_b, stream);
     if (e) return e;
     return check_launch("wgrad_tc_partial");
+}
+
+extern "C" int dgmc_wgrad_tc_partial(const float* g, int64_t ldg, const float* x, int64_t ldx, int64_t k,
+                                     int m, int n, float* partial, float* partial_b, dgmc_stream_t stream) {
+    return wgrad_tc_partial_impl(g, ldg, x, ldx, k, m, n, k, partial, partial_b, stream);
+}
+
+extern "C" int dgmc_wgrad_tc_partial_rows(const float* g, int64_t ldg, const float* x, int64_t ldx, int64_t k,
+                                          int m, int n, int64_t bias_rows, float* partial, float* partial_b,
+                                          dgmc_stream_t stream) {
+    DGMC_REQUIRE(bias_rows >= 0 && bias_rows <= k, "wgrad_tc_partial_rows: bias_rows out of range");
+    return wgrad_tc_partial_impl(g, ldg, x, ldx, k, m, n, bias_rows, partial, partial_b, stream);
 }

@@ -214,8 +214,10 @@ class DGMC(torch.nn.Module):
                 # which K6 reads (and whose gradient its backward writes) as one tensor
                 o = self.psi_2(torch.cat([r_s.view(B * N_s, R_in), r_t], dim=0), merged.edge_index,
                                merged.edge_attr)
-                p = ops.node_linear(o, w1, key=('mlp0', id(self)))
-                S_hat = ops.diff_mlp_merged(S_hat, p, B * N_s, b1, w2, b2, cand)
+                # b1 belongs to the source rows: added by the GEMM epilogue, its gradient summed by
+                # the weight-gradient kernel (no separate add / column-sum kernels)
+                p = ops.node_linear(o, w1, b1, key=('mlp0', id(self)), bias_rows=B * N_s)
+                S_hat = ops.diff_mlp_merged(S_hat, p, B * N_s, None, w2, b2, cand)
                 continue
             p_s, p_t = consensus_nodes(r_s, r_t)
             S_hat = ops.diff_mlp(S_hat, p_s, p_t, w2, b2, cand)

@@ -348,7 +348,7 @@ class _DiffMLPMerged(torch.autograd.Function):
     @staticmethod
     def forward(ctx, s_hat, p, b1, w2, b2, cand, n_s):
         s_hat, p, w2, b2 = _f32(s_hat), _f32(p), _f32(w2), _f32(b2)
-        ps = p[:n_s] + b1
+        ps = p[:n_s] + b1 if b1 is not None else p[:n_s]   # None: already added by the GEMM (bias_rows)
         pt = p[n_s:]
         out = torch.empty_like(s_hat)
         call('dgmc_diff_mlp_fwd', s_hat, ps, pt, cand.idx, w2, b2, out, cand.m, cand.k, ps.size(1),
@@ -373,7 +373,7 @@ class _DiffMLPMerged(torch.autograd.Function):
         ws2 = _workspace(query('dgmc_balanced_workspace', perm.numel(), r), g.device)
         call('dgmc_diff_mlp_bwd_targets_balanced', g, ps, pt, tptr, seg_of, perm, w2, d_pt,
              cand.targets, perm.numel(), cand.k, r, ws2, ws2.numel(), stream_ptr())
-        d_b1 = d_ps.sum(0) if ctx.needs_input_grad[2] else None
+        d_b1 = d_ps.sum(0) if ctx.needs_input_grad[2] else None   # b1 is None: no gradient asked
         return g, d_p, d_b1, d_w2, d_b2, None, None
 
 
@@ -460,11 +460,16 @@ def _split_weight(weight, transposed, holder=None, slot=None):
     return ws
 
 
-def _linear_tc(x, split, bias, relu, n_out, k_in, out=None):
-    """`out`: optional [rows, n_out] row-strided destination (e.g. a column block of a wider buffer)."""
+def _linear_tc(x, split, bias, relu, n_out, k_in, out=None, bias_rows=None):
+    """`out`: optional [rows, n_out] row-strided destination (e.g. a column block of a wider buffer);
+    `bias_rows`: add the bias to the first bias_rows rows only."""
     y = torch.empty(x.size(0), n_out, dtype=torch.float32, device=x.device) if out is None else out
-    call('dgmc_linear_tc', RowStrided(x), x.stride(0), split, bias, int(relu), RowStrided(y), y.stride(0),
-         x.size(0), n_out, k_in, stream_ptr())
+    if bias_rows is None or bias is None:
+        call('dgmc_linear_tc', RowStrided(x), x.stride(0), split, bias, int(relu), RowStrided(y), y.stride(0),
+             x.size(0), n_out, k_in, stream_ptr())
+    else:
+        call('dgmc_linear_tc_rows', RowStrided(x), x.stride(0), split, bias, int(bias_rows), int(relu),
+             RowStrided(y), y.stride(0), x.size(0), n_out, k_in, stream_ptr())
     return y
 
 
@@ -492,13 +497,19 @@ def _wgrad_tc_chunked(a, b):
 class _NodeLinear(torch.autograd.Function):
     """kn = False: weight [out, in] (torch Linear); kn = True: weight [in, out] (SplineConv)."""
     @staticmethod
-    def forward(ctx, x, weight, bias, relu, group, kn, out):
+    def forward(ctx, x, weight, bias, relu, group, kn, out, bias_rows):
         k_in, n_out = (weight.size(0), weight.size(1)) if kn else (weight.size(1), weight.size(0))
         if _linear_tc_ok(x, n_out, k_in):
-            y = _linear_tc(x, _split_weight(weight, kn, group, 'split_fwd'), bias, relu, n_out, k_in, out)
+            y = _linear_tc(x, _split_weight(weight, kn, group, 'split_fwd'), bias, relu, n_out, k_in, out,
+                           bias_rows)
         else:
             w_kn = weight if kn else weight.t()
-            if relu:  # bias + ReLU in the library GEMM's epilogue
+            if bias_rows is not None and bias is not None:
+                y = x @ w_kn
+                y[:bias_rows] += bias
+                if relu:
+                    y = torch.relu_(y)
+            elif relu:  # bias + ReLU in the library GEMM's epilogue
                 y = torch._addmm_activation(bias, x, w_kn, use_gelu=False)
             else:
                 y = torch.addmm(bias, x, w_kn) if bias is not None else x @ w_kn
@@ -510,6 +521,7 @@ class _NodeLinear(torch.autograd.Function):
         else:
             ctx.save_for_backward(x, weight)
         ctx.has_bias, ctx.relu, ctx.group, ctx.kn = bias is not None, relu, group, kn
+        ctx.bias_rows = bias_rows if bias is not None else None
         if group is not None:
             ctx.slot = group.calls
             group.calls += 1
@@ -546,7 +558,7 @@ class _NodeLinear(torch.autograd.Function):
         want_w = ctx.needs_input_grad[1]
         want_b = ctx.has_bias and ctx.needs_input_grad[2]
         if not (want_w or want_b):
-            return dx, None, None, None, None, None, None
+            return dx, None, None, None, None, None, None, None
         if kn or weight.numel() > 64 * 1024 or k < 2048:
             # not a "tiny output, long reduction" shape: no grouping across consensus steps; the
             # tensor-core split-K kernel in chunks of 128 output channels when TMA can read the
@@ -557,8 +569,8 @@ class _NodeLinear(torch.autograd.Function):
                 if dw is None:
                     dw = a.t() @ b
             if want_b:
-                db = g.sum(0)
-            return dx, dw, db, None, None, None, None
+                db = g.sum(0) if ctx.bias_rows is None else g[:ctx.bias_rows].sum(0)
+            return dx, dw, db, None, None, None, None, None
         m, n = n_out, k_in
         grp = ctx.group
         # tcgen05 3xTF32 kernel on TMA-loaded MN-major tiles when the operands meet TMA's alignment
@@ -567,6 +579,7 @@ class _NodeLinear(torch.autograd.Function):
                                               g.data_ptr(), x.data_ptr()))
         fn_splits = 'dgmc_wgrad_tc_splits' if tc else 'dgmc_wgrad_splits'
         fn_partial = 'dgmc_wgrad_tc_partial' if tc else 'dgmc_wgrad_partial'
+        rows_bias = ctx.bias_rows is not None      # bias gradient over the leading rows only
         calls, slot = (1, 0) if grp is None else (grp.calls, ctx.slot)
         holder = grp if grp is not None else WGradGroup()
         if holder.partial is None:
@@ -576,10 +589,16 @@ class _NodeLinear(torch.autograd.Function):
             holder.partial_b = torch.empty(calls * holder.splits, m, dtype=torch.float32,
                                            device=g.device) if ctx.has_bias else None
         off = slot * holder.splits
-        call(fn_partial, g, g.stride(0), RowStrided(x), x.stride(0), k, m, n,
-             holder.partial[off:off + holder.splits],
-             None if holder.partial_b is None else holder.partial_b[off:off + holder.splits],
-             stream_ptr())
+        pb = None if holder.partial_b is None else holder.partial_b[off:off + holder.splits]
+        if rows_bias and tc:
+            call('dgmc_wgrad_tc_partial_rows', g, g.stride(0), RowStrided(x), x.stride(0), k, m, n,
+                 int(ctx.bias_rows), holder.partial[off:off + holder.splits], pb, stream_ptr())
+        else:
+            call(fn_partial, g, g.stride(0), RowStrided(x), x.stride(0), k, m, n,
+                 holder.partial[off:off + holder.splits], pb, stream_ptr())
+            if rows_bias:   # the FFMA kernel sums all rows: overwrite its bias partials
+                pb.zero_()
+                pb[0] = g[:ctx.bias_rows].sum(0)
         holder.done += 1
         if holder.done == calls:  # last backward of this weight: reduce everything once
             dw = torch.empty_like(weight)
@@ -589,24 +608,24 @@ class _NodeLinear(torch.autograd.Function):
             holder.partial = holder.partial_b = None
             holder.split_fwd = holder.split_bwd = None
             holder.done = 0  # a second backward over a retained graph starts afresh
-        return dx, dw, db, None, None, None, None
+        return dx, dw, db, None, None, None, None, None
 
 
-def node_linear(x, weight, bias=None, relu=False, key=None, kn=False, out=None):
+def node_linear(x, weight, bias=None, relu=False, key=None, kn=False, out=None, bias_rows=None):
     """relu?(x [nodes, in] @ W + bias) with W = weight[out, in]^T (kn=False) or weight[in, out]
     (kn=True).  Forward and input gradient run on the tensor-core kernel dgmc_linear_tc (3xTF32,
     bias and ReLU in its epilogue) whenever x meets TMA's alignment rules, else on the library GEMM;
     the weight / bias gradient (a reduction over all nodes with a tiny output) runs on the split-K
     kernel dgmc_wgrad when the output is small, else stays with the library.  `out`: write the
     result into this row-strided [nodes, out] view (a column block of a layer buffer) instead of a
-    fresh tensor."""
+    fresh tensor.  `bias_rows`: the bias belongs to the first bias_rows nodes only."""
     if x.is_cuda and x.dtype == torch.float32 and x.dim() == 2 and x.stride(1) == 1 \
             and weight.dtype == torch.float32 and (bias is not None or not relu):
         group = None
         if key is not None and _DEFER[0] is not None and torch.is_grad_enabled():
             group = _DEFER[0].setdefault((key, x.size(0), tuple(weight.shape)), WGradGroup())
-        return _NodeLinear.apply(x, weight, bias, relu, group, kn, out)
-    assert out is None, 'node_linear(out=...) is a CUDA fp32 feature'
+        return _NodeLinear.apply(x, weight, bias, relu, group, kn, out, bias_rows)
+    assert out is None and bias_rows is None, 'node_linear(out=..., bias_rows=...) are CUDA fp32 features'
     y = torch.addmm(bias, x, weight) if (kn and bias is not None) else (
         x @ weight if kn else torch.nn.functional.linear(x, weight, bias))
     return torch.relu(y) if relu else y

@@ -206,6 +206,10 @@ int dgmc_wgrad_tc_supported(int m, int n, int64_t ldg, int64_t ldx, const float*
 int dgmc_wgrad_tc_splits(int64_t k, int m, int n);
 int dgmc_wgrad_tc_partial(const float* g, int64_t ldg, const float* x, int64_t ldx, int64_t k, int m, int n,
                           float* partial, float* partial_b, dgmc_stream_t stream);
+/* Same with the bias gradient summed over rows [0, bias_rows) of g only (see dgmc_linear_tc_rows). */
+int dgmc_wgrad_tc_partial_rows(const float* g, int64_t ldg, const float* x, int64_t ldx, int64_t k, int m,
+                               int n, int64_t bias_rows, float* partial, float* partial_b,
+                               dgmc_stream_t stream);
 
 /* out[i, 0:c] = y[i, 0:c] > 0 ? g[i, 0:c] : 0 on row-strided operands (column blocks of wider
  * buffers): the ReLU backward between two RelConv layers (rel.py:84-85) when the activations live in
@@ -228,6 +232,12 @@ int dgmc_linear_tc_split_weight(const float* w, int64_t ldw, int transposed, int
                                 void* workspace, size_t workspace_bytes, dgmc_stream_t stream);
 int dgmc_linear_tc(const float* x, int64_t ldx, const void* split_weight, const float* bias, int relu,
                    float* y, int64_t ldy, int64_t rows, int n_out, int k_in, dgmc_stream_t stream);
+/* Same with the bias added to rows [0, bias_rows) only: the first consensus-MLP layer on the merged
+ * node table [source rows ; target rows], whose bias belongs to the source side (Lin1(o_s - o_t) =
+ * (W1 o_s + b1) - W1 o_t, dgmc.py:219-221). */
+int dgmc_linear_tc_rows(const float* x, int64_t ldx, const void* split_weight, const float* bias,
+                        int64_t bias_rows, int relu, float* y, int64_t ldy, int64_t rows, int n_out, int k_in,
+                        dgmc_stream_t stream);
 
 /* ---- dense branch: consensus update without materialising D [B, N_s, N_t, R] ----------------
  * s_out[b,i,j] = s_in[b,i,j] + [s_mask[b,i] & t_mask[b,j]] * (b2 + sum_c w2[c] relu(ps[b,i,c] - pt[b,j,c]))

@@ -105,3 +105,28 @@ def test_node_linear_autograd(kn, relu, rows, n_in, n_out):
     assert (y.double() - ref).abs().max().item() <= 2e-6 * ref.abs().max().item()
     for a, r_ in ((x.grad, xr.grad), (w.grad, wr.grad), (b.grad, br.grad)):
         assert (a.double() - r_).abs().max().item() <= 2e-5 * r_.abs().max().item() + 1e-6
+
+
+@pytest.mark.parametrize('rows,n_in,n_out,tc_wgrad', [(5000, 64, 64, True),    # tensor-core forward + weight gradient
+                                                      (5000, 64, 64, False),   # FFMA weight gradient
+                                                      (700, 32, 16, True)])    # few rows: library weight gradient
+def test_node_linear_bias_on_leading_rows(rows, n_in, n_out, tc_wgrad, monkeypatch):
+    """bias_rows: the bias (first consensus-MLP layer on the merged node table) belongs to the
+    source rows only — forward and bias gradient against fp64 autograd."""
+    from dgmc import ops
+    monkeypatch.setattr(ops, 'WGRAD_TENSOR_CORE', tc_wgrad)
+    g = torch.Generator().manual_seed(17)
+    n_b = rows // 3
+    x = torch.randn(rows, n_in, generator=g).to(DEV).requires_grad_()
+    w = (torch.randn(n_out, n_in, generator=g) * 0.1).to(DEV).requires_grad_()
+    b = torch.randn(n_out, generator=g).to(DEV).requires_grad_()
+    go = torch.randn(rows, n_out, generator=g).to(DEV)
+    y = ops.node_linear(x, w, b, bias_rows=n_b)
+    y.backward(go)
+    xr, wr, br = [t.detach().double().requires_grad_() for t in (x, w, b)]
+    ref = xr @ wr.t()
+    ref = torch.cat([ref[:n_b] + br, ref[n_b:]], dim=0)
+    ref.backward(go.double())
+    assert (y.double() - ref).abs().max().item() <= 2e-6 * ref.abs().max().item()
+    for a, r_ in ((x.grad, xr.grad), (w.grad, wr.grad), (b.grad, br.grad)):
+        assert (a.double() - r_).abs().max().item() <= 2e-5 * r_.abs().max().item() + 1e-6
