@@ -241,11 +241,12 @@ class RowShardedDGMC(DGMC):
                 p_t = all_gather_rows(_pad_rows(p_loc[sp.ns_loc:], sp.nt_max), self.group)[sp.pos_t]
                 S_hat = ops.diff_mlp(S_hat, p_s_loc, p_t, w2, b2, cand)
                 continue
-            if merged is not None:
-                o = self.psi_2(torch.cat([r_s, r_t], dim=0), merged.edge_index, merged.edge_attr)
-                p = ops.node_linear(o, w1, key=('mlp0', id(self)))
-                p_s, p_t = p[:N_s] + b1, p[N_s:]
-            S_hat = ops.diff_mlp(S_hat, p_s[lo:hi], p_t, w2, b2, cand)
+            # psi_2 replicated on the merged pair (this package's RelCNN / SplineCNN without batch-norm
+            # statistics or dropout); K6 on this rank's source rows of the merged node table
+            assert merged is not None, 'RowShardedDGMC needs a psi_2 that runs on the merged pair'
+            o = self.psi_2(torch.cat([r_s, r_t], dim=0), merged.edge_index, merged.edge_attr)
+            p = ops.node_linear(o, w1, b1, key=('mlp0', id(self)), bias_rows=N_s)
+            S_hat = ops.diff_mlp_merged(S_hat, p, N_s, None, w2, b2, cand, rows=(lo, hi))
         S_L = ops.softmax_k(S_hat)
         S_idx = S_idx.view(n_loc, k)
 

@@ -342,28 +342,34 @@ class _DiffMLP(torch.autograd.Function):
 
 class _DiffMLPMerged(torch.autograd.Function):
     """_DiffMLP on ONE node table p = [source rows ; target rows] (psi_2 ran on the merged pair) with
-    the first-layer bias b1 added to the source rows here.  The backward writes d_ps and d_pt into
-    the two row blocks of a single d_p, so autograd does not have to zero-pad and add two slice
-    gradients (two fills, two copies and an add of [N_s + N_t, R] per consensus step)."""
+    the first-layer bias b1 added to the source rows here (b1 = None: the GEMM already did).  The
+    backward writes d_ps and d_pt into the row blocks of a single d_p, so autograd does not have to
+    zero-pad and add two slice gradients (two fills, two copies and an add of [N_s + N_t, R] per
+    consensus step).  rows = (lo, hi): the source rows this call owns (row sharding); the other
+    source rows get a zero gradient."""
     @staticmethod
-    def forward(ctx, s_hat, p, b1, w2, b2, cand, n_s):
+    def forward(ctx, s_hat, p, b1, w2, b2, cand, n_s, lo, hi):
         s_hat, p, w2, b2 = _f32(s_hat), _f32(p), _f32(w2), _f32(b2)
-        ps = p[:n_s] + b1 if b1 is not None else p[:n_s]   # None: already added by the GEMM (bias_rows)
+        ps = p[lo:hi] + b1 if b1 is not None else p[lo:hi]
         pt = p[n_s:]
         out = torch.empty_like(s_hat)
         call('dgmc_diff_mlp_fwd', s_hat, ps, pt, cand.idx, w2, b2, out, cand.m, cand.k, ps.size(1),
              stream_ptr())
-        ctx.cand, ctx.n_s = cand, n_s
+        ctx.cand, ctx.rows = cand, (n_s, lo, hi)
         ctx.save_for_backward(ps, pt, w2)
         return out
 
     @staticmethod
     def backward(ctx, g):
         ps, pt, w2 = ctx.saved_tensors
-        cand, n_s, g = ctx.cand, ctx.n_s, _f32(g)
+        cand, (n_s, lo, hi), g = ctx.cand, ctx.rows, _f32(g)
         r = ps.size(1)
         d_p = torch.empty(n_s + pt.size(0), r, dtype=torch.float32, device=g.device)
-        d_ps, d_pt = d_p[:n_s], d_p[n_s:]
+        if lo > 0:
+            d_p[:lo].zero_()
+        if hi < n_s:
+            d_p[hi:n_s].zero_()
+        d_ps, d_pt = d_p[lo:hi], d_p[n_s:]
         d_w2 = torch.empty_like(w2)
         d_b2 = torch.empty(1, dtype=torch.float32, device=g.device)
         ws = _workspace(query('dgmc_diff_mlp_bwd_workspace', cand.m, r), g.device)
@@ -374,13 +380,15 @@ class _DiffMLPMerged(torch.autograd.Function):
         call('dgmc_diff_mlp_bwd_targets_balanced', g, ps, pt, tptr, seg_of, perm, w2, d_pt,
              cand.targets, perm.numel(), cand.k, r, ws2, ws2.numel(), stream_ptr())
         d_b1 = d_ps.sum(0) if ctx.needs_input_grad[2] else None   # b1 is None: no gradient asked
-        return g, d_p, d_b1, d_w2, d_b2, None, None
+        return g, d_p, d_b1, d_w2, d_b2, None, None, None, None
 
 
-def diff_mlp_merged(s_hat, p, n_s, b1, w2, b2, cand):
-    """diff_mlp(s_hat, p[:n_s] + b1, p[n_s:], w2, b2, cand) for a merged node table p [n_s + n_t, R4]."""
-    assert cand.m == n_s and p.size(0) == n_s + cand.targets
-    return _DiffMLPMerged.apply(s_hat, p, b1, w2, b2, cand, n_s)
+def diff_mlp_merged(s_hat, p, n_s, b1, w2, b2, cand, rows=None):
+    """diff_mlp(s_hat, p[lo:hi] + b1, p[n_s:], w2, b2, cand) for a merged node table p [n_s + n_t, R4];
+    rows = (lo, hi) defaults to all n_s source rows."""
+    lo, hi = (0, n_s) if rows is None else rows
+    assert cand.m == hi - lo and p.size(0) == n_s + cand.targets
+    return _DiffMLPMerged.apply(s_hat, p, b1, w2, b2, cand, n_s, lo, hi)
 
 
 def diff_mlp(s_hat, ps, pt, w2, b2, cand):
