@@ -263,7 +263,11 @@ class RowShardedDGMC(DGMC):
     def _local(self, S, y):
         lo, hi = S.__rows__
         mine = (y[0] >= lo) & (y[0] < hi)
-        rows = (y[0] - lo).clamp(0, max(hi - lo - 1, 0))
+        # ground truths of other ranks are masked out by `mine`; point them at DISTINCT local rows:
+        # thousands of duplicates of one clamped row made the backward of the row gather (a sorted,
+        # serialised index_put accumulate) take 0.45 ms
+        spread = torch.arange(y.size(1), device=y.device) % max(hi - lo, 1)
+        rows = torch.where(mine, y[0] - lo, spread)
         return mine, rows
 
     def loss(self, S, y, reduction='mean'):
