@@ -130,6 +130,24 @@ class DGMC(torch.nn.Module):
             w1, b1, w2 = F.pad(w1, (0, 0, 0, pad)), F.pad(b1, (0, pad)), F.pad(w2, (0, pad))
         return w1, b1, w2, b2
 
+    def _psi_2_then_lin1(self, x0, merged, w1, b1, n_source):
+        """P = Lin1(psi_2(x0)) on the merged node table, with b1 on the source rows only.  When
+        psi_2 ends in its own Lin (RelCNN(lin=True)), the two linear maps have nothing in between:
+        P = feats (W1 W_f)^T + W1 b_f (+ b1), one GEMM instead of two (and one input-gradient and
+        one weight-gradient GEMM less per consensus step).  W1 b_f is the same for source and target
+        rows and cancels in Lin1(o_s - o_t) (dgmc.py:219-221) — which is also why the reference's
+        gradient of psi_2.final.bias is exactly zero; it is kept in the graph with weight 0 so that
+        the parameter still receives that zero gradient."""
+        from .rel import RelCNN
+        psi = self.psi_2
+        if isinstance(psi, RelCNN) and psi.lin:
+            feats = psi(x0, merged.edge_index, merged.edge_attr, features_only=True)
+            w_eff, b_eff = ops.region_cached(('lin1_final', id(self)), lambda: (
+                w1 @ psi.final.weight, b1 + 0.0 * (w1 @ psi.final.bias)))
+            return ops.node_linear(feats, w_eff, b_eff, key=('lin1_final', id(self)), bias_rows=n_source)
+        o = psi(x0, merged.edge_index, merged.edge_attr)
+        return ops.node_linear(o, w1, b1, key=('mlp0', id(self)), bias_rows=n_source)
+
     def forward(self, x_s, edge_index_s, edge_attr_s, batch_s, x_t, edge_index_t, edge_attr_t,
                 batch_t, y=None):
         # psi_2 and the consensus MLP are applied num_steps times with the same weights: their
@@ -212,11 +230,10 @@ class DGMC(torch.nn.Module):
             if merged is not None and s_mask is None and t_mask is None:
                 # one un-padded pair: psi_2 and the hoisted first MLP layer on the merged node table,
                 # which K6 reads (and whose gradient its backward writes) as one tensor
-                o = self.psi_2(torch.cat([r_s.view(B * N_s, R_in), r_t], dim=0), merged.edge_index,
-                               merged.edge_attr)
                 # b1 belongs to the source rows: added by the GEMM epilogue, its gradient summed by
                 # the weight-gradient kernel (no separate add / column-sum kernels)
-                p = ops.node_linear(o, w1, b1, key=('mlp0', id(self)), bias_rows=B * N_s)
+                x0 = torch.cat([r_s.view(B * N_s, R_in), r_t], dim=0)
+                p = self._psi_2_then_lin1(x0, merged, w1, b1, B * N_s)
                 S_hat = ops.diff_mlp_merged(S_hat, p, B * N_s, None, w2, b2, cand)
                 continue
             p_s, p_t = consensus_nodes(r_s, r_t)

@@ -77,7 +77,7 @@ class RelCNN(torch.nn.Module):
                 and x.is_cuda and x.dtype == torch.float32 and x.dim() == 2
                 and self.in_channels % 4 == 0 and self.convs[0].out_channels % 4 == 0)
 
-    def _forward_direct(self, x, edge_index):
+    def _forward_direct(self, x, edge_index, features_only=False):
         c_in, c_out = self.in_channels, self.convs[0].out_channels
         buf = torch.empty(x.size(0), c_in + self.num_layers * c_out, dtype=torch.float32, device=x.device)
         cur, parts, off = ops.copy_into(x, buf, 0), [], c_in
@@ -86,13 +86,20 @@ class RelCNN(torch.nn.Module):
             parts.append(alias)
             off += c_out
         parts.append(cur)
+        # the gradient of `out` comes from this package's own GEMM backward (the final Lin, or the
+        # caller's fused map when features_only) unless the features are the module's output
         out = ops.join_slices(buf, self.lin, *parts)
-        return ops.node_linear(out, self.final.weight, self.final.bias, key=('final', id(self))) \
-            if self.lin else out
+        if features_only or not self.lin:
+            return out
+        return ops.node_linear(out, self.final.weight, self.final.bias, key=('final', id(self)))
 
-    def forward(self, x, edge_index, *args):
+    def forward(self, x, edge_index, *args, features_only=False):
+        """features_only: return the input of the final Lin (the concatenated layer outputs) instead
+        of applying it — DGMC folds that Lin into the first consensus-MLP layer (two linear maps
+        with nothing in between)."""
+        assert not features_only or self.lin
         if self._direct_cat(x):
-            return self._forward_direct(x, edge_index)
+            return self._forward_direct(x, edge_index, features_only)
         feats = [x]
         for conv, norm in zip(self.convs, self.batch_norms):
             h = conv(feats[-1], edge_index, relu=True)
@@ -100,8 +107,9 @@ class RelCNN(torch.nn.Module):
                 h = norm(h)
             feats.append(F.dropout(h, p=self.dropout, training=self.training))
         out = torch.cat(feats, dim=-1) if self.cat else feats[-1]
-        return ops.node_linear(out, self.final.weight, self.final.bias, key=('final', id(self))) \
-            if self.lin else out
+        if features_only or not self.lin:
+            return out
+        return ops.node_linear(out, self.final.weight, self.final.bias, key=('final', id(self)))
 
     def __repr__(self):
         return ('{}({}, {}, num_layers={}, batch_norm={}, cat={}, lin={}, dropout={})').format(

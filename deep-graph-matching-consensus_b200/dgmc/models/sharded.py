@@ -244,8 +244,7 @@ class RowShardedDGMC(DGMC):
             # psi_2 replicated on the merged pair (this package's RelCNN / SplineCNN without batch-norm
             # statistics or dropout); K6 on this rank's source rows of the merged node table
             assert merged is not None, 'RowShardedDGMC needs a psi_2 that runs on the merged pair'
-            o = self.psi_2(torch.cat([r_s, r_t], dim=0), merged.edge_index, merged.edge_attr)
-            p = ops.node_linear(o, w1, b1, key=('mlp0', id(self)), bias_rows=N_s)
+            p = self._psi_2_then_lin1(torch.cat([r_s, r_t], dim=0), merged, w1, b1, N_s)
             S_hat = ops.diff_mlp_merged(S_hat, p, N_s, None, w2, b2, cand, rows=(lo, hi))
         S_L = ops.softmax_k(S_hat)
         S_idx = S_idx.view(n_loc, k)
