@@ -77,6 +77,32 @@ class GraphCSR(object):
     _cache = {}
 
     def __init__(self, edge_index, num_nodes):
+        self._build(edge_index, num_nodes)
+
+    @classmethod
+    def union(cls, edge_index, g_a, g_b):
+        """GraphCSR of the disjoint union (edge_index = [a's edges, b's edges shifted]) that takes its
+        RelConv operator from the parts (no sort); the adjacency arrays themselves are only built
+        if something else (SplineConv, GIN) asks for them."""
+        self = cls.__new__(cls)
+        self.num_nodes = g_a.num_nodes + g_b.num_nodes
+        self.num_edges = g_a.num_edges + g_b.num_edges
+        self._rel = _RelOperator.concat(g_a.rel, g_b.rel)
+        self._lazy = edge_index
+        return self
+
+    def __getattr__(self, name):
+        # only reached for attributes that are not set: the adjacency arrays of a union() graph
+        lazy = self.__dict__.get('_lazy')
+        if lazy is None or name.startswith('__'):
+            raise AttributeError(name)
+        rel = self.__dict__.get('_rel')
+        self.__dict__['_lazy'] = None
+        self._build(lazy, self.num_nodes)
+        self._rel = rel
+        return self.__dict__[name] if name in self.__dict__ else object.__getattribute__(self, name)
+
+    def _build(self, edge_index, num_nodes):
         src = edge_index[0].to(torch.int32).contiguous()
         dst = edge_index[1].to(torch.int32).contiguous()
         self.num_nodes, self.num_edges = num_nodes, src.numel()
@@ -97,6 +123,12 @@ class GraphCSR(object):
         return self._rel
 
     @classmethod
+    def seed(cls, edge_index, num_nodes, graph):
+        key = (edge_index.data_ptr(), tuple(edge_index.shape), edge_index._version, num_nodes,
+               str(edge_index.device))
+        cls._cache[key] = (edge_index, graph)
+
+    @classmethod
     def of(cls, edge_index, num_nodes):
         key = (edge_index.data_ptr(), tuple(edge_index.shape), edge_index._version, num_nodes,
                str(edge_index.device))
@@ -110,6 +142,26 @@ class GraphCSR(object):
 
 
 class _RelOperator(object):
+    @classmethod
+    def concat(cls, a, b):
+        """Operator of the disjoint union of two graphs (b's nodes numbered after a's) from the two
+        operators: block-diagonal, so the CSRs are concatenations with shifted indices — no sort."""
+        self = cls.__new__(cls)
+        self.n_out = self.n_in = a.n_out + b.n_out
+        n_a = a.n_out
+
+        def join(ptr_a, ptr_b, src_a, src_b, w_a, w_b, seg_a, seg_b, src_shift, seg_shift):
+            nnz_a = src_a.numel()
+            return (torch.cat([ptr_a[:-1], ptr_b + nnz_a]), torch.cat([src_a, src_b + src_shift]),
+                    torch.cat([w_a, w_b]), torch.cat([seg_a[:nnz_a], seg_b + seg_shift]))
+        # forward operator [3N, N]: segments = 3 rows per node, sources = node ids
+        self.f_ptr, self.f_src, self.f_w, self.f_seg = join(a.f_ptr, b.f_ptr, a.f_src, b.f_src, a.f_w, b.f_w,
+                                                            a.f_seg, b.f_seg, n_a, 3 * n_a)
+        # its transpose [N, 3N]: segments = node ids, sources = rows of the forward operator
+        self.b_ptr, self.b_src, self.b_w, self.b_seg = join(a.b_ptr, b.b_ptr, a.b_src, b.b_src, a.b_w, b.b_w,
+                                                            a.b_seg, b.b_seg, 3 * n_a, n_a)
+        return self
+
     def __init__(self, graph):
         n, dev = graph.num_nodes, graph.in_ptr.device
         self.n_out = self.n_in = n
@@ -131,9 +183,14 @@ class MergedPair(object):
     RelCNN / SplineCNN without active batch-norm statistics or dropout."""
     _cache = {}
 
-    def __init__(self, e_s, e_t, ea_s, ea_t, n_s):
+    def __init__(self, e_s, e_t, ea_s, ea_t, n_s, n_t=None):
         self.edge_index = torch.cat([e_s, e_t + n_s], dim=1)
         self.edge_attr = None if ea_s is None else torch.cat([ea_s, ea_t], dim=0)
+        if n_t is not None:
+            # the union's RelConv operator is the concatenation of the parts' (usually already built
+            # for psi_1): seed the GraphCSR cache so that psi_2 does not sort the merged edge list
+            g = GraphCSR.union(self.edge_index, GraphCSR.of(e_s, n_s), GraphCSR.of(e_t, n_t))
+            GraphCSR.seed(self.edge_index, n_s + n_t, g)
 
     @staticmethod
     def mergeable(psi, training):
@@ -155,7 +212,7 @@ class MergedPair(object):
         if hit is None or any(a is not b for a, b in zip(hit[0], tensors)):
             if len(cls._cache) > 64:
                 cls._cache.clear()
-            hit = (tensors, cls(e_s, e_t, ea_s, ea_t, n_s))
+            hit = (tensors, cls(e_s, e_t, ea_s, ea_t, n_s, n_t if ea_s is None else None))
             cls._cache[key] = hit
         return hit[1]
 
