@@ -77,36 +77,34 @@ class GraphCSR(object):
     _cache = {}
 
     def __init__(self, edge_index, num_nodes):
-        self._build(edge_index, num_nodes)
+        # edge lists now; the sorted adjacency arrays only when something reads them (SplineConv, GIN:
+        # RelConv works from `rel`, which sorts its own operator)
+        self.num_nodes, self.num_edges = num_nodes, edge_index.size(1)
+        self.src = edge_index[0].to(torch.int32).contiguous()
+        self.dst = edge_index[1].to(torch.int32).contiguous()
+        self._lazy = True
 
     @classmethod
     def union(cls, edge_index, g_a, g_b):
         """GraphCSR of the disjoint union (edge_index = [a's edges, b's edges shifted]) that takes its
-        RelConv operator from the parts (no sort); the adjacency arrays themselves are only built
-        if something else (SplineConv, GIN) asks for them."""
-        self = cls.__new__(cls)
-        self.num_nodes = g_a.num_nodes + g_b.num_nodes
-        self.num_edges = g_a.num_edges + g_b.num_edges
+        RelConv operator from the parts (no sort)."""
+        self = cls(edge_index, g_a.num_nodes + g_b.num_nodes)
         self._rel = _RelOperator.concat(g_a.rel, g_b.rel)
-        self._lazy = edge_index
         return self
 
-    def __getattr__(self, name):
-        # only reached for attributes that are not set: the adjacency arrays of a union() graph
-        lazy = self.__dict__.get('_lazy')
-        if lazy is None or name.startswith('__'):
-            raise AttributeError(name)
-        rel = self.__dict__.get('_rel')
-        self.__dict__['_lazy'] = None
-        self._build(lazy, self.num_nodes)
-        self._rel = rel
-        return self.__dict__[name] if name in self.__dict__ else object.__getattribute__(self, name)
+    _ADJACENCY = ('in_ptr', 'in_edge', 'in_seg', 'out_ptr', 'out_edge', 'out_seg', 'in_nbr', 'out_nbr',
+                  'inv_in', 'inv_out')
 
-    def _build(self, edge_index, num_nodes):
-        src = edge_index[0].to(torch.int32).contiguous()
-        dst = edge_index[1].to(torch.int32).contiguous()
-        self.num_nodes, self.num_edges = num_nodes, src.numel()
-        self.src, self.dst = src, dst
+    def __getattr__(self, name):
+        # only reached for attributes that are not set yet: build the adjacency arrays on first use
+        if name in GraphCSR._ADJACENCY and self.__dict__.get('_lazy'):
+            self.__dict__['_lazy'] = False
+            self._build_adjacency()
+            return self.__dict__[name]
+        raise AttributeError(name)
+
+    def _build_adjacency(self):
+        src, dst, num_nodes = self.src, self.dst, self.num_nodes
         self.in_ptr, self.in_edge, self.in_seg = csr_build(dst, num_nodes, True)
         self.out_ptr, self.out_edge, self.out_seg = csr_build(src, num_nodes, True)
         self.in_nbr = src[self.in_edge.long()].contiguous()
@@ -163,13 +161,21 @@ class _RelOperator(object):
         return self
 
     def __init__(self, graph):
-        n, dev = graph.num_nodes, graph.in_ptr.device
+        n, dev = graph.num_nodes, graph.src.device
         self.n_out = self.n_in = n
         src, dst = graph.src, graph.dst
         node = torch.arange(n, dtype=torch.int32, device=dev)
         rows = torch.cat([3 * node, 3 * dst + 1, 3 * src + 2])          # segment of A
         cols = torch.cat([node, src, dst])
-        w = torch.cat([torch.ones(n, device=dev), graph.inv_in[dst.long()], graph.inv_out[src.long()]])
+        # 1 / max(degree, 1) from edge counts (integer histograms: exact, order-independent)
+        # (scatter_add on integers rather than bincount, which sizes its result with a host sync)
+        src_l, dst_l = src.long(), dst.long()
+        one = torch.ones(src.numel(), dtype=torch.int32, device=dev)
+        deg_in = torch.zeros(n, dtype=torch.int32, device=dev).scatter_add_(0, dst_l, one)
+        deg_out = torch.zeros(n, dtype=torch.int32, device=dev).scatter_add_(0, src_l, one)
+        inv_in = deg_in.clamp_(min=1).to(torch.float32).reciprocal_()
+        inv_out = deg_out.clamp_(min=1).to(torch.float32).reciprocal_()
+        w = torch.cat([torch.ones(n, device=dev), inv_in[dst_l], inv_out[src_l]])
         self.f_ptr, perm, self.f_seg = csr_build(rows, 3 * n, True)
         self.f_src, self.f_w = cols[perm.long()].contiguous(), w[perm.long()].contiguous()
         self.b_ptr, perm, self.b_seg = csr_build(cols, n, True)
