@@ -251,7 +251,7 @@ NCU_TRAFFIC_DBP15K = {
 }
 
 
-def kernel_rooflines(w, model, e_t, peaks, step_ms, iters=5):
+def kernel_rooflines(w, model, e_t, peaks, step_ms, iters=5, e_s=None):
     """Times each hot kernel alone (cold L2) on step-shaped data.  Algorithmic bytes / flops per
     launch follow SURVEY.md §8(d): `bytes_min` (every operand read once, every result written once)
     when the gathered table fits in L2, else `bytes_logical` (gathered rows counted per access)."""
@@ -273,8 +273,16 @@ def kernel_rooflines(w, model, e_t, peaks, step_ms, iters=5):
     S = torch.rand(n_s, k_eff, generator=g).to(dev)
     r_s, p_s, p_t, x_t = rnd(n_s, R), rnd(n_s, R), rnd(n_t, R), rnd(n_t, R)
     w2, b2 = rnd(R), torch.zeros(1, device=dev)
-    graph_t = ops.GraphCSR.of(e_t, n_t)
-    E = e_t.size(1)
+    # K5 as the step runs it: psi_2 aggregates on the MERGED pair (source + target graph), once per
+    # layer in the forward and once (the transposed operator, same kernel) in the backward pass
+    if e_s is not None:
+        e_m = torch.cat([e_s, e_t + n_s], dim=1)
+        n_m5, k5_name, k5_calls = n_s + n_t, 'merged pair', 2 * L * T
+    else:
+        e_m, n_m5, k5_name, k5_calls = e_t, n_t, 'target graph', L * T
+    graph_t = ops.GraphCSR.of(e_m, n_m5)
+    x_m5 = rnd(n_m5, R)
+    E = e_m.size(1)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     hbm, tf = peaks['hbm_gbs'], peaks['bf16_tflops']
     rows = []
@@ -310,9 +318,9 @@ def kernel_rooflines(w, model, e_t, peaks, step_ms, iters=5):
                      8 * n_s * k_eff + 4 * R * n_s * (1 + 2 * k_eff))
         add('K4 transport (balanced segmented gather by target)', lambda: ops.transport(S, r_s, cand), T,
             wk, 'hbm', b)
-        wk, b = pick(n_t * 4 * R, 8 * n_t * R + 8 * E + 8 * n_t, 8 * n_t * R + 2 * E * (4 * R + 4))
-        add('K5 rel_aggregate ([3N,N] sparse product, target graph)',
-            lambda: ops.rel_aggregate(x_t, graph_t), L * T, wk, 'hbm', b)
+        wk, b = pick(n_m5 * 4 * R, 8 * n_m5 * R + 8 * E + 8 * n_m5, 8 * n_m5 * R + 2 * E * (4 * R + 4))
+        add('K5 rel_aggregate ([3N,N] sparse product, %s)' % k5_name,
+            lambda: ops.rel_aggregate(x_m5, graph_t), k5_calls, wk, 'hbm', b)
         wk, b = pick(n_t * 4 * R, 4 * R * (n_s + n_t) + 12 * n_s * k_eff,
                      4 * R * n_s * (1 + k_eff) + 12 * n_s * k_eff)
         add('K6 diff_mlp fwd', lambda: ops.diff_mlp(S, p_s, p_t, w2, b2, cand), T, wk, 'hbm', b)
@@ -648,7 +656,7 @@ def main():
     out = None
     if rank == 0:
         peaks = load_peaks()
-        rl = kernel_rooflines(w, model, d['e_t'], peaks, ms_per_step)
+        rl = kernel_rooflines(w, model, d['e_t'], peaks, ms_per_step, e_s=d['e_s'])
         top = max(rl, key=lambda r: r['share_of_step'])
         roofline = {k_: top[k_] for k_ in ('bound', 'achieved', 'peak', 'unit', 'frac', 'traffic')}
         roofline.update(kernel=top['kernel'], peak_source=peaks['source'] + ' (burst: kernel timed alone)')

@@ -189,6 +189,131 @@ __global__ void __launch_bounds__(256, NV == 1 ? 5 : 1) balanced_main_kernel(con
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Lean MODE 0 kernel for rows of up to 128 channels (one float4 per lane).  Same blocks, same pieces,
+// same partial slots and same summation order as balanced_main_kernel<G, 1, 0> — bit-identical
+// results — but everything that depends only on the ENTRY (does a segment end here, where does its
+// sum go: output row or partial slot, is there a gap of empty segments behind it) is worked out ONCE
+// by the lane that holds the entry's metadata and travels with the shuffles, instead of being
+// re-derived by all lanes at every entry.  ncu on the general kernel at the DBP15K shape: 71 warp
+// instructions per entry step, 5.6 % of them FFMA, issue slots 69 % busy — the gather was
+// instruction-bound, not memory-bound.
+// ---------------------------------------------------------------------------------------------
+// rows s0 .. s1-1 of `out` (channels 4q .. 4q+3 of this lane) = 0: the empty segments in a gap.  Rare
+// and kept out of line so that it costs the hot loop neither registers nor code.
+__device__ __noinline__ void lean_zero_rows(float* outq, long long ldo, long long s0, long long s1) {
+    for (long long s = s0; s < s1; ++s)
+        *reinterpret_cast<float4*>(outq + s * ldo) = make_float4(0, 0, 0, 0);
+}
+
+template <int G, bool ACC, bool SCALE>
+__global__ void __launch_bounds__(256, 5) balanced_lean_kernel(const BalArgs a) {
+    constexpr int PER = CB / G;
+    constexpr int BR = 4;
+    constexpr int GPW = 32 / G;                       // groups per warp
+    const int lane = threadIdx.x & 31, gl = lane % G;
+    const long long warps = (long long)gridDim.x * (blockDim.x >> 5);
+    const long long nblk = (a.nnz + CB - 1) / CB;
+    const int r = a.r4 * 4;
+    const bool live = gl < a.r4;                      // lanes beyond the row width only take part in shuffles
+    const float* __restrict__ xq = a.x + 4 * gl;
+    float* __restrict__ outq = a.out + 4 * gl;
+    float* __restrict__ partq = a.partial + 4 * gl;
+    const int src_div = a.src_div;
+    const long long ldx = a.ldx, ldo = a.ldo;
+
+    // All lanes of a warp run the same number of iterations (full-mask shuffles below): the loop runs
+    // over WARP-sized sets of GPW consecutive blocks; a group whose block lies beyond the end works
+    // on zero entries.
+    for (long long wb = ((long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * GPW; wb < nblk;
+         wb += warps * GPW) {
+        const long long b = wb + lane / G;
+        const long long e_begin = b * CB;
+        const int count = b < nblk ? (int)(a.nnz - e_begin < CB ? a.nnz - e_begin : CB) : 0;
+        int before = -1, after = -1, first_seg = -1;
+        if (count > 0) {
+            before = e_begin > 0 ? __ldg(a.seg_of + e_begin - 1) : -1;
+            after = e_begin + count < a.nnz ? __ldg(a.seg_of + e_begin + count) : -1;
+            first_seg = __ldg(a.seg_of + e_begin);
+        }
+        // ---- metadata of the entries this lane holds: source row, weight, and what happens AFTER the
+        //      entry (flag 1: the segment's piece ends, its sum goes to element offset `off` of the
+        //      output (flag 2 clear) or of the partial buffer (flag 2 set); flag 4: a gap of empty
+        //      segments follows) ----
+        int m_row[PER], m_flag[PER], m_off[PER]; float m_w[PER];
+#pragma unroll
+        for (int p = 0; p < PER; ++p) {
+            const int j = gl + p * G;
+            const long long e = e_begin + j;
+            int row = 0, flag = 0, off = 0; float we = 0.f;
+            if (j < count) {
+                const int sg = __ldg(a.seg_of + e);
+                const int nx = j + 1 < count ? __ldg(a.seg_of + e + 1) : -2;
+                const int sv = __ldg(a.src + e);
+                row = src_div > 1 ? sv / src_div : sv;
+                we = a.w ? __ldg(a.w + (a.w_index ? __ldg(a.w_index + e) : (int)e)) : 1.f;
+                if (a.src_scale) we *= __ldg(a.src_scale + row);
+                if (nx != sg) {
+                    const bool open_left = sg == first_seg && sg == before;
+                    const bool open_right = nx == -2 && sg == after;
+                    const bool complete = !open_left && !open_right;
+                    flag = 1 | (complete ? 0 : 2) | ((nx > sg + 1) ? 4 : 0);
+                    off = complete ? (int)((long long)sg * ldo)
+                                   : (int)((2 * b + (sg == first_seg ? 0 : 1)) * (long long)r);
+                }
+            }
+            m_row[p] = row; m_w[p] = we; m_flag[p] = flag; m_off[p] = off;
+        }
+        if (!ACC && live && count > 0 && before != first_seg)
+            lean_zero_rows(outq, ldo, (long long)before + 1, first_seg);
+
+        float4 acc = make_float4(0, 0, 0, 0);
+        // ---- stream the rows, BR at a time; control flow is the same for the whole warp ----
+#pragma unroll
+        for (int batch = 0; batch < CB / BR; ++batch) {
+            int rows[BR], fl[BR], of[BR]; float wt[BR]; float4 t[BR];
+#pragma unroll
+            for (int u = 0; u < BR; ++u) {
+                const int j = batch * BR + u;              // compile-time after unrolling
+                rows[u] = __shfl_sync(0xffffffffu, m_row[j / G], j % G, G);
+                wt[u] = __shfl_sync(0xffffffffu, m_w[j / G], j % G, G);
+                fl[u] = __shfl_sync(0xffffffffu, m_flag[j / G], j % G, G);
+                of[u] = __shfl_sync(0xffffffffu, m_off[j / G], j % G, G);
+            }
+#pragma unroll
+            for (int u = 0; u < BR; ++u)                   // entries beyond `count` read row 0 and are ignored
+                t[u] = live ? ldg4(xq + (size_t)rows[u] * ldx) : make_float4(0, 0, 0, 0);
+#pragma unroll
+            for (int u = 0; u < BR; ++u) {
+                const int j = batch * BR + u;
+                if (j < count) {
+                    acc.x += wt[u] * t[u].x; acc.y += wt[u] * t[u].y;
+                    acc.z += wt[u] * t[u].z; acc.w += wt[u] * t[u].w;
+                }
+                if (fl[u] & 1) {
+                    const bool to_partial = fl[u] & 2;
+                    float4 o = acc;
+                    if (SCALE && !to_partial) {
+                        const float sc = __ldg(a.seg_scale + __ldg(a.seg_of + e_begin + j));
+                        o.x *= sc; o.y *= sc; o.z *= sc; o.w *= sc;
+                    }
+                    if (live) {
+                        float4* dst = reinterpret_cast<float4*>((to_partial ? partq : outq) + of[u]);
+                        if (ACC && !to_partial) { const float4 q = *dst; o.x += q.x; o.y += q.y; o.z += q.z; o.w += q.w; }
+                        *dst = o;
+                    }
+                    acc = make_float4(0, 0, 0, 0);
+                    if (!ACC && (fl[u] & 4) && live)       // empty segments behind this one (rare)
+                        lean_zero_rows(outq, ldo, (long long)__ldg(a.seg_of + e_begin + j) + 1,
+                                       __ldg(a.seg_of + e_begin + j + 1));
+                }
+            }
+        }
+        if (!ACC && live && count > 0 && e_begin + count >= a.nnz)     // trailing empty segments
+            lean_zero_rows(outq, ldo, (long long)__ldg(a.seg_of + a.nnz - 1) + 1, a.n_seg);
+    }
+}
+
 // One lane group per entry block: if the block holds the FIRST piece of a segment that runs on into
 // later blocks, add that segment's pieces up in block order and write the result.
 template <int G, int NV>
@@ -251,6 +376,27 @@ static int launch_balanced(const BalArgs& a, cudaStream_t stream) {
     if (nblk == 0) {
         if (!a.accumulate) balanced_zero_kernel<<<wave_grid(a.n_seg * a.r4, 256, 8), 256, 0, stream>>>(a);
         return check_launch("balanced segmented reduction (empty)", a.accumulate ? 0 : 1);
+    }
+    if (MODE == 0 && a.r4 <= 32 && a.n_seg * a.ldo < (1ll << 31) && 2 * nblk * (a.r4 * 4ll) < (1ll << 31)) {
+        // rows of up to 128 channels, element offsets that fit 32 bits: the lean kernel (same pieces
+        // and slots, same fix-up pass)
+        const int G = a.r4 <= 8 ? 8 : (a.r4 <= 16 ? 16 : 32);
+        const int grid = wave_grid(nblk, 256 / G, 8);
+#define LEAN(G_, ACC_, SCALE_) balanced_lean_kernel<G_, ACC_, SCALE_><<<grid, 256, 0, stream>>>(a)
+#define LEAN_G(G_)                                                                                  \
+    do {                                                                                            \
+        if (a.accumulate) { if (a.seg_scale) LEAN(G_, true, true); else LEAN(G_, true, false); }    \
+        else { if (a.seg_scale) LEAN(G_, false, true); else LEAN(G_, false, false); }               \
+    } while (0)
+        if (G == 8) LEAN_G(8); else if (G == 16) LEAN_G(16); else LEAN_G(32);
+#undef LEAN_G
+#undef LEAN
+        if (nblk > 1) {
+            if (G == 8) balanced_fixup_kernel<8, 1><<<wave_grid(nblk, 32, 8), 256, 0, stream>>>(a, 1);
+            else if (G == 16) balanced_fixup_kernel<16, 1><<<wave_grid(nblk, 16, 8), 256, 0, stream>>>(a, 1);
+            else balanced_fixup_kernel<32, 1><<<wave_grid(nblk, 8, 8), 256, 0, stream>>>(a, 1);
+        }
+        return check_launch("balanced segmented reduction", nblk > 1 ? 2 : 1);
     }
 #define BAL(G, NV)                                                                                  \
     do {                                                                                            \
