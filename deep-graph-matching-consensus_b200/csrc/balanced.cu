@@ -240,12 +240,14 @@ __global__ void __launch_bounds__(256, 5) balanced_lean_kernel(const BalArgs a) 
         //      entry (flag 1: the segment's piece ends, its sum goes to element offset `off` of the
         //      output (flag 2 clear) or of the partial buffer (flag 2 set); flag 4: a gap of empty
         //      segments follows) ----
-        int m_row[PER], m_flag[PER], m_off[PER]; float m_w[PER];
+        //      packed into one word: bit 31 = piece ends, bit 0 = to the partial buffer, bit 1 = gap; the
+        //      offsets are multiples of 4 (float4 rows) and below 2^31, so those bits are free
+        int m_row[PER], m_act[PER]; float m_w[PER];
 #pragma unroll
         for (int p = 0; p < PER; ++p) {
             const int j = gl + p * G;
             const long long e = e_begin + j;
-            int row = 0, flag = 0, off = 0; float we = 0.f;
+            int row = 0, act = 0; float we = 0.f;
             if (j < count) {
                 const int sg = __ldg(a.seg_of + e);
                 const int nx = j + 1 < count ? __ldg(a.seg_of + e + 1) : -2;
@@ -257,12 +259,12 @@ __global__ void __launch_bounds__(256, 5) balanced_lean_kernel(const BalArgs a) 
                     const bool open_left = sg == first_seg && sg == before;
                     const bool open_right = nx == -2 && sg == after;
                     const bool complete = !open_left && !open_right;
-                    flag = 1 | (complete ? 0 : 2) | ((nx > sg + 1) ? 4 : 0);
-                    off = complete ? (int)((long long)sg * ldo)
-                                   : (int)((2 * b + (sg == first_seg ? 0 : 1)) * (long long)r);
+                    const int off = complete ? (int)((long long)sg * ldo)
+                                             : (int)((2 * b + (sg == first_seg ? 0 : 1)) * (long long)r);
+                    act = (int)(0x80000000u | (unsigned)off | (complete ? 0u : 1u) | ((nx > sg + 1) ? 2u : 0u));
                 }
             }
-            m_row[p] = row; m_w[p] = we; m_flag[p] = flag; m_off[p] = off;
+            m_row[p] = row; m_w[p] = we; m_act[p] = act;
         }
         if (!ACC && live && count > 0 && before != first_seg)
             lean_zero_rows(outq, ldo, (long long)before + 1, first_seg);
@@ -271,14 +273,13 @@ __global__ void __launch_bounds__(256, 5) balanced_lean_kernel(const BalArgs a) 
         // ---- stream the rows, BR at a time; control flow is the same for the whole warp ----
 #pragma unroll
         for (int batch = 0; batch < CB / BR; ++batch) {
-            int rows[BR], fl[BR], of[BR]; float wt[BR]; float4 t[BR];
+            int rows[BR], act[BR]; float wt[BR]; float4 t[BR];
 #pragma unroll
             for (int u = 0; u < BR; ++u) {
                 const int j = batch * BR + u;              // compile-time after unrolling
                 rows[u] = __shfl_sync(0xffffffffu, m_row[j / G], j % G, G);
                 wt[u] = __shfl_sync(0xffffffffu, m_w[j / G], j % G, G);
-                fl[u] = __shfl_sync(0xffffffffu, m_flag[j / G], j % G, G);
-                of[u] = __shfl_sync(0xffffffffu, m_off[j / G], j % G, G);
+                act[u] = __shfl_sync(0xffffffffu, m_act[j / G], j % G, G);
             }
 #pragma unroll
             for (int u = 0; u < BR; ++u)                   // entries beyond `count` read row 0 and are ignored
@@ -290,20 +291,20 @@ __global__ void __launch_bounds__(256, 5) balanced_lean_kernel(const BalArgs a) 
                     acc.x += wt[u] * t[u].x; acc.y += wt[u] * t[u].y;
                     acc.z += wt[u] * t[u].z; acc.w += wt[u] * t[u].w;
                 }
-                if (fl[u] & 1) {
-                    const bool to_partial = fl[u] & 2;
+                if (act[u] < 0) {                          // bit 31: the segment's piece ends here
+                    const bool to_partial = act[u] & 1;
                     float4 o = acc;
                     if (SCALE && !to_partial) {
                         const float sc = __ldg(a.seg_scale + __ldg(a.seg_of + e_begin + j));
                         o.x *= sc; o.y *= sc; o.z *= sc; o.w *= sc;
                     }
                     if (live) {
-                        float4* dst = reinterpret_cast<float4*>((to_partial ? partq : outq) + of[u]);
+                        float4* dst = reinterpret_cast<float4*>((to_partial ? partq : outq) + (act[u] & 0x7ffffffc));
                         if (ACC && !to_partial) { const float4 q = *dst; o.x += q.x; o.y += q.y; o.z += q.z; o.w += q.w; }
                         *dst = o;
                     }
                     acc = make_float4(0, 0, 0, 0);
-                    if (!ACC && (fl[u] & 4) && live)       // empty segments behind this one (rare)
+                    if (!ACC && (act[u] & 2) && live)      // empty segments behind this one (rare)
                         lean_zero_rows(outq, ldo, (long long)__ldg(a.seg_of + e_begin + j) + 1,
                                        __ldg(a.seg_of + e_begin + j + 1));
                 }
