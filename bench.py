@@ -246,6 +246,8 @@ NCU_TRAFFIC_DBP15K = {
     'K1': 19.98e6 + 47.37e6,  # topk_tc_kernel + topk_merge_kernel (r1f/r1j captures; the two cast
                               # kernels, 40 MB fp32 in / 20 MB bf16 out, were not captured)
     'K6': 13.08e6,            # diff_mlp_fwd_kernel<16,1> (r1f capture)
+    'K5': 15.14e6,            # balanced_lean_kernel<16>, merged pair, forward operator (r1w capture; the
+                              # transposed operator reads 34.3 MB; fix-up kernel 5.5 MB, not included)
     'G1': 30.04e6,            # linear_tc_kernel<64,2>, 38,960 x 192 -> 64 (r1n capture: X once; y stays in L2)
     'G2': 39.96e6,            # wgrad_tc_kernel<64> (r1n capture: G and X once; the reduce kernel not captured)
 }
