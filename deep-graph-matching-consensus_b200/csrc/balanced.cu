@@ -327,27 +327,50 @@ __global__ void __launch_bounds__(256) balanced_fixup_kernel(const BalArgs a, in
         const long long e_begin = b * CB;
         const long long e_end = e_begin + CB < a.nnz ? e_begin + CB : a.nnz;
         if (e_end >= a.nnz) continue;                           // last block: nothing runs on
+        // the four boundary ids are independent loads: issue them together (this kernel is a chain of
+        // global-memory latencies, nothing else)
         const int s = __ldg(a.seg_of + e_end - 1);
-        if (__ldg(a.seg_of + e_end) != s) continue;             // last segment ends with the block
-        const bool whole = __ldg(a.seg_of + e_begin) == s;      // the piece starts at the block start
-        if (whole && e_begin > 0 && __ldg(a.seg_of + e_begin - 1) == s) continue;  // not the first piece
+        const int s_next = __ldg(a.seg_of + e_end);
+        const int s_first = __ldg(a.seg_of + e_begin);
+        const int s_prev = e_begin > 0 ? __ldg(a.seg_of + e_begin - 1) : -1;
+        const long long nb2 = e_end + CB;                        // first entry of the block after next
+        const int s_next2 = nb2 < a.nnz ? __ldg(a.seg_of + nb2) : -1;
+        if (s_next != s) continue;                              // last segment ends with the block
+        const bool whole = s_first == s;                        // the piece starts at the block start
+        if (whole && s_prev == s) continue;                     // not the first piece
         float4 acc[NV];
+        // first two pieces (the common case: a segment cut once) loaded together
+        float4 t0[NV], t1[NV];
+        const long long slot0 = 2 * b + (whole ? 0 : 1), slot1 = 2 * (b + 1);
 #pragma unroll
-        for (int v = 0; v < NV; ++v) acc[v] = make_float4(0, 0, 0, 0);
-        long long slot = 2 * b + (whole ? 0 : 1);
-        for (long long bb = b;;) {
-#pragma unroll
-            for (int v = 0; v < NV; ++v) {
-                const int q = gl + v * G;
-                if (q < a.r4) {
-                    const float4 t = *reinterpret_cast<const float4*>(a.partial + (size_t)slot * r + 4 * q);
-                    acc[v].x += t.x; acc[v].y += t.y; acc[v].z += t.z; acc[v].w += t.w;
-                }
+        for (int v = 0; v < NV; ++v) {
+            const int q = gl + v * G;
+            t0[v] = t1[v] = make_float4(0, 0, 0, 0);
+            if (q < a.r4) {
+                t0[v] = *reinterpret_cast<const float4*>(a.partial + (size_t)slot0 * r + 4 * q);
+                t1[v] = *reinterpret_cast<const float4*>(a.partial + (size_t)slot1 * r + 4 * q);
             }
-            ++bb;
-            const long long nb = bb * CB;                        // first entry of the next block
-            if (nb >= a.nnz || __ldg(a.seg_of + nb) != s) break;
-            slot = 2 * bb;
+        }
+#pragma unroll
+        for (int v = 0; v < NV; ++v) {
+            acc[v] = make_float4(0, 0, 0, 0);
+            acc[v].x += t0[v].x; acc[v].y += t0[v].y; acc[v].z += t0[v].z; acc[v].w += t0[v].w;
+            acc[v].x += t1[v].x; acc[v].y += t1[v].y; acc[v].z += t1[v].z; acc[v].w += t1[v].w;
+        }
+        if (s_next2 == s) {                                     // a hub: the segment runs on
+            for (long long bb = b + 2;; ++bb) {
+                const long long slot = 2 * bb;
+#pragma unroll
+                for (int v = 0; v < NV; ++v) {
+                    const int q = gl + v * G;
+                    if (q < a.r4) {
+                        const float4 t = *reinterpret_cast<const float4*>(a.partial + (size_t)slot * r + 4 * q);
+                        acc[v].x += t.x; acc[v].y += t.y; acc[v].z += t.z; acc[v].w += t.w;
+                    }
+                }
+                const long long nb = (bb + 1) * CB;              // first entry of the next block
+                if (nb >= a.nnz || __ldg(a.seg_of + nb) != s) break;
+            }
         }
         const float sc = (apply_seg_scale && a.seg_scale) ? __ldg(a.seg_scale + s) : 1.f;
 #pragma unroll
