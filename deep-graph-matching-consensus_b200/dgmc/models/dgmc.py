@@ -185,8 +185,9 @@ class DGMC(torch.nn.Module):
                 # union (same arithmetic per node, half the launches, twice the GEMM height)
                 o = self.psi_2(torch.cat([r_s, r_t], dim=0), merged.edge_index, merged.edge_attr)
                 p = ops.node_linear(o, w1, key=('mlp0', id(self)))
-                p_s, p_t = p[:r_s.size(0)] + b1, p[r_s.size(0):]
-                return _repad(p_s, s_mask), _repad(p_t, t_mask)
+                # b1 after re-padding: the reference applies mlp[0] to padded source rows too (their
+                # o_s is 0, so they see relu(b1 - W1 o_t), dgmc.py:217-223)
+                return _repad(p[:r_s.size(0)], s_mask) + b1, _repad(p[r_s.size(0):], t_mask)
             o_s = self.psi_2(r_s, edge_index_s, edge_attr_s)
             o_t = self.psi_2(r_t, edge_index_t, edge_attr_t)
             o_s, o_t = _repad(o_s, s_mask), _repad(o_t, t_mask)

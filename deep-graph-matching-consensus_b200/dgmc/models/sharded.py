@@ -157,6 +157,10 @@ def sharded_relcnn(psi, x_gathered, sp, group):
         weight = ops.region_cached(('relconv', id(conv)), lambda c=conv: torch.cat(
             [c.root.weight, c.lin1.weight, c.lin2.weight], dim=1))
         h = ops.node_linear(stacked, weight, conv.root.bias, relu=True, key=('relconv', id(conv)))
+        if psi.batch_norm:
+            # only reached in eval mode (MergedPair.mergeable): the running-statistics affine map
+            # is per node, so the node shard applies it without communication (rel.py:86-87)
+            h = psi.batch_norms[i](h)
         feats.append(h)
         if i + 1 < len(psi.convs):
             full = all_gather_rows(_pad_rows(h, sp.n_max), group)

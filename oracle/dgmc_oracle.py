@@ -24,7 +24,9 @@ Model description: a "psi spec" is a dict
 and parameters come as a flat {name: tensor} dict using the reference's state_dict names
 (`psi_1.convs.0.lin1.weight`, `mlp.0.weight`, ...).  Random draws are INJECTED (`draws`)
 rather than generated, so that oracle, reference and CUDA path see identical indicator
-functions and negatives whatever device or dtype they run in.
+functions and negatives whatever device or dtype they run in.  The functions are device-agnostic
+plain torch: tests may also evaluate them in fp32 ON the GPU (ATen / cuBLAS arithmetic) to measure
+the reference formulas' own fp32 noise on that hardware (parity mode (i)).
 """
 import math
 
@@ -50,14 +52,14 @@ def pad_batch(x, batch):
 
     -> (dense [B, N_max, C] zero-filled, mask [B, N_max] bool)."""
     if batch is None:
-        return x.unsqueeze(0), torch.ones(1, x.size(0), dtype=torch.bool)
+        return x.unsqueeze(0), torch.ones(1, x.size(0), dtype=torch.bool, device=x.device)
     B = int(batch.max()) + 1
     sizes = torch.bincount(batch, minlength=B)
     n_max = int(sizes.max())
     start = torch.cumsum(sizes, 0) - sizes
-    local = torch.arange(batch.numel()) - start[batch]
+    local = torch.arange(batch.numel(), device=x.device) - start[batch]
     dense = x.new_zeros(B, n_max, x.size(1))
-    mask = torch.zeros(B, n_max, dtype=torch.bool)
+    mask = torch.zeros(B, n_max, dtype=torch.bool, device=x.device)
     dense[batch, local] = x
     mask[batch, local] = True
     return dense, mask
@@ -306,7 +308,7 @@ def dgmc_forward(spec1, spec2, p, x_s, edge_index_s, edge_attr_s, batch_s, x_t, 
                 S_idx = torch.cat([S_idx, neg], dim=-1)
             S_idx = include_gt(S_idx, s_mask, y)
     k_eff = S_idx.size(-1)
-    rows_b = torch.arange(B).view(B, 1, 1)
+    rows_b = torch.arange(B, device=h_s.device).view(B, 1, 1)
     cand = h_t[rows_b, S_idx]  # [B, N_s, k_eff, C]   (gather, dgmc.py:198-200)
     logits = (h_s.unsqueeze(2) * cand).sum(dim=-1)  # dgmc.py:201
     S_0 = logits.softmax(dim=-1)[s_mask]

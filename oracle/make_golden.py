@@ -227,6 +227,22 @@ def main():
     make_case('gin_batched_dense', g1, g2, inp, y, 1, -1, True, loss_on='0', seed=12345)
     make_case('gin_batched_sparse_kN', g1, g2, inp, y, 1, 4, True, loss_on='0', seed=12345)
 
+    # -- ragged SPARSE batch with a RelCNN psi_2 and two consensus steps: the reference leaves padded
+    #    source rows in play (they hold uniform S and scatter into real targets)
+    #    and applies the consensus MLP to them, so the second step sees what they contributed.
+    #    k = N_t(max) selects every column, which makes the candidate SETS independent of tie order.
+    xs, eis, _, bs = batched(gen, [5, 7, 6], 3, 12)
+    xt, eit, _, bt = batched(gen, [6, 7, 5], 3, 12)
+    inp = dict(x_s=xs, edge_index_s=eis, edge_attr_s=None, batch_s=bs, x_t=xt, edge_index_t=eit,
+               edge_attr_t=None, batch_t=bt)
+    y = torch.stack([torch.arange(18), torch.tensor([0, 1, 2, 3, 4, 6, 5, 4, 3, 2, 1, 0,
+                                                     0, 1, 2, 3, 4, 0])])
+    q1 = dict(kind='rel', **{'in': 12}, out=16, layers=2, batch_norm=False, cat=True, lin=True,
+              dropout=0.0)
+    q2 = dict(kind='rel', **{'in': 8}, out=8, layers=2, batch_norm=False, cat=True, lin=True,
+              dropout=0.0)
+    make_case('ragged_sparse_rel_kN', q1, q2, inp, y, 2, 7, True, loss_on='L', seed=4)
+
 
 if __name__ == '__main__':
     main()

