@@ -2,9 +2,11 @@
 
 RelConv computes root(x_i) + mean_{j->i} lin1(x_j) + mean_{i->j} lin2(x_j) (rel.py:25-31).  The
 mean commutes with the linear maps, so the B200 path aggregates the raw features in both flow
-directions with one CSR segmented-gather each (`ops.rel_aggregate`, deterministic, no atomics)
-and then applies ONE library GEMM [N, 3*C_in] x [3*C_in, C_out] with the three weight matrices
-side by side.  Parameter names (lin1, lin2, root, batch_norms, final) match the reference's
+directions ([x | mean_in x | mean_out x], one sparse [3N, N] product, deterministic, no atomics)
+and applies ONE tensor-core GEMM [N, 3*C_in] x [3*C_in, C_out] with the three weight matrices side
+by side (`ops.node_linear`: tcgen05 3xTF32, bias + ReLU in the epilogue).  Where the shape allows
+(C_in a multiple of 32, C_out <= 64: psi_2) both happen in ONE kernel, `ops.relconv_fused`: the
+aggregated operand is gathered straight into the GEMM's shared-memory stage.  Parameter names (lin1, lin2, root, batch_norms, final) match the reference's
 state_dict so checkpoints interchange."""
 import torch
 import torch.nn.functional as F
@@ -30,6 +32,13 @@ class RelConv(torch.nn.Module):
         fused into the GEMM epilogue.  out: write the result into this column block of a layer
         buffer; passthrough: also return x as handed through the aggregation (ops._RelAggregatePass)."""
         graph = ops.GraphCSR.of(edge_index, x.size(0))
+        if ops.relconv_fused_ok(x, graph.rel, self.out_channels):
+            # aggregation and GEMM in one kernel (dgmc_relconv_tc)
+            weight = ops.region_cached(('relconv', id(self)), lambda: torch.cat(
+                [self.root.weight, self.lin1.weight, self.lin2.weight], dim=1))
+            y, alias = ops.relconv_fused(x, weight, self.root.bias, graph.rel, relu=relu,
+                                         key=('relconv', id(self)), out=out)
+            return (y, alias) if passthrough else y
         if passthrough:
             stacked, alias = ops.rel_aggregate_pass(x, graph)
         else:

@@ -239,6 +239,29 @@ int dgmc_linear_tc_rows(const float* x, int64_t ldx, const void* split_weight, c
                         int64_t bias_rows, int relu, float* y, int64_t ldy, int64_t rows, int n_out, int k_in,
                         dgmc_stream_t stream);
 
+/* ---- fused RelConv layer: aggregation -> tensor-core GEMM in one kernel -------------------------
+ * y[i, :] = relu?( [ x_i | sum_{e in seg(3i+1)} w_e x[src_e] | sum_{e in seg(3i+2)} w_e x[src_e] ] W^T + bias )
+ *           (+ addend[i, :])
+ * replaces RelConv.forward (rel.py:25-31: root(x) + mean-propagate(lin1 x) + mean-propagate(lin2 x),
+ * the two PyG propagate calls and three Linear maps) and, with the operator of the transposed
+ * aggregation and the block-transposed weight, its input gradient.  ptr [3 rows + 1] / src / w: CSR
+ * with three segments per node — 3i: the node itself (one entry, weight 1; read through TMA, the list
+ * is not consulted), 3i+1 / 3i+2: the two weighted neighbour lists (mean aggregation: w = 1 / degree).
+ * order [ceil(rows / 32) * 32]: for every group of 32 consecutive rows a permutation of 0..31, rows
+ * with the longest lists first (any permutation is correct; this one balances the gather rounds of a
+ * warp).
+ * split_weight: dgmc_linear_tc_split_weight(W [n_out, 3c]).  stacked (nullable) receives the fp32
+ * operand rows [rows, 3c] for the weight gradient; addend (nullable, may alias y) is added before the
+ * store.  c = 32 or 64 (the split weight stays resident in shared memory), n_out <= 64, x / stacked /
+ * addend with 16-byte aligned bases and pitches
+ * (dgmc_relconv_tc_supported).  3xTF32 arithmetic as dgmc_linear_tc. */
+int dgmc_relconv_tc_supported(int64_t rows, int c, int n_out, int64_t ldx, const float* x);
+int dgmc_relconv_tc(const int32_t* ptr, const int32_t* src, const float* w, const int32_t* order,
+                    const float* x, int64_t ldx,
+                    const void* split_weight, const float* bias, int relu, const float* addend, int64_t lda,
+                    float* stacked, int64_t lds, float* y, int64_t ldy, int64_t rows, int c, int n_out,
+                    dgmc_stream_t stream);
+
 /* ---- dense branch: consensus update without materialising D [B, N_s, N_t, R] ----------------
  * s_out[b,i,j] = s_in[b,i,j] + [s_mask[b,i] & t_mask[b,j]] * (b2 + sum_c w2[c] relu(ps[b,i,c] - pt[b,j,c]))
  * replaces D = o_s[:, :, None] - o_t[:, None], mlp(D).masked_fill(~S_mask, 0) at dgmc.py:178-179
