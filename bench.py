@@ -10,7 +10,8 @@ DBP15K zh_en-shaped pair (19,388 x 19,572 nodes, 300-d features, RelCNN 300->256
 64->64 L3).  Prints ONE JSON line (contract in the task statement).  `value` is measured with
 inputs resident in HBM; `e2e` through the public API with pinned HOST inputs copied every step
 and the loss read back.  `--impl reference` times the CPU oracle port of the reference
-(oracle/dgmc_oracle.py; the Python reference itself cannot travel to the GPU box).
+(the unmodified reference package from oracle/_ref — copied there, git-ignored, by oracle/make_ref.py
+in the build container — else the oracle port oracle/dgmc_oracle.py).
 """
 import argparse
 import json
@@ -123,13 +124,64 @@ def oracle_specs(w):
     return s1, s2
 
 
-def cpu_reference_steps(w, inputs, steps, warmup, budget_s):
-    """Times the oracle port (reference algorithm, torch CPU ops, all host threads) on the same
-    workload.  Returns (steps_per_s, steps_timed, cores, seconds_per_step)."""
+REF_DIR = os.path.join(ROOT, 'oracle', '_ref')
+
+
+def _reference_step_fn(w, inputs):
+    """One training step of the UNMODIFIED reference package (oracle/_ref/dgmc, copied from
+    /root/reference by oracle/make_ref.py), imported in a way that cannot collide with the product
+    package of the same name: examples/dbp15k.py:37-47 — zero_grad, forward(train, y), loss(S_L),
+    backward, Adam.  torch_geometric / torch_scatter come from the stand-ins in oracle/shims/ (not
+    installable offline).  One deviation, which SURVEY.md §8(c) prescribes: DGMC.__top_k__'s non-KeOps
+    route materialises [N_s, N_t, C] = 388.6 GB at this shape, so it is replaced by the same arithmetic
+    done per row chunk (matmul + topk)."""
+    import importlib
+    saved_path, saved_mods = list(sys.path), {k: v for k, v in sys.modules.items() if k == 'dgmc' or k.startswith('dgmc.')}
+    for k in saved_mods:
+        del sys.modules[k]
+    sys.path[:0] = [REF_DIR, os.path.join(ROOT, 'oracle', 'shims')]
+    try:
+        ref = importlib.import_module('dgmc')
+        assert os.path.realpath(ref.__file__).startswith(os.path.realpath(REF_DIR)), ref.__file__
+        from dgmc.models import DGMC, RelCNN
+    finally:
+        sys.path[:] = saved_path
+
+    def chunked_top_k(self, x_s, x_t):
+        out = []
+        for lo in range(0, x_s.size(1), 2048):
+            out.append((x_s[:, lo:lo + 2048] @ x_t.transpose(-1, -2)).topk(self.k, dim=2)[1])
+        return torch.cat(out, dim=1)
+    DGMC.__top_k__ = chunked_top_k
+    torch.manual_seed(0)
+    psi_1 = RelCNN(w['feat'], w['dim'], w['layers'], batch_norm=False, cat=True, lin=True, dropout=0.5)
+    psi_2 = RelCNN(w['rnd_dim'], w['rnd_dim'], w['layers'], batch_norm=False, cat=True, lin=True, dropout=0.0)
+    model = DGMC(psi_1, psi_2, num_steps=w['num_steps'], k=w['k'], detach=True)
+    model.train()
+    opt = torch.optim.Adam(model.parameters(), lr=1e-3)
+    import warnings
+
+    def one_step():
+        opt.zero_grad()
+        with warnings.catch_warnings():
+            warnings.simplefilter('ignore')
+            _, S_L = model(inputs['x_s'], inputs['e_s'], None, None, inputs['x_t'], inputs['e_t'], None, None,
+                           inputs['y'])
+            loss = model.loss(S_L, inputs['y'])
+        loss.backward()
+        opt.step()
+        return loss.item()
+    # leave the reference's modules out of sys.modules again: the GPU arm imports the product's `dgmc`
+    for k in [k for k in sys.modules if k == 'dgmc' or k.startswith('dgmc.')]:
+        del sys.modules[k]
+    sys.modules.update(saved_mods)
+    return one_step
+
+
+def _port_step_fn(w, inputs):
+    """The oracle port (oracle/dgmc_oracle.py) of the same step — used when oracle/_ref is absent."""
     import torch.nn.functional as F
     from oracle import dgmc_oracle as O
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
     s1, s2 = oracle_specs(w)
     params = {k: v.requires_grad_(True) for k, v in O.init_dgmc(0, s1, s2).items()}
     opt = torch.optim.Adam(list(params.values()), lr=1e-3)
@@ -148,6 +200,23 @@ def cpu_reference_steps(w, inputs, steps, warmup, budget_s):
         loss.backward()
         opt.step()
         return loss.item()
+    return one_step
+
+
+def cpu_reference_steps(w, inputs, steps, warmup, budget_s):
+    """Times the reference's CPU implementation of the step on all host threads: the unmodified
+    reference package from oracle/_ref when it is there (kind 'reference'), else the oracle port (kind
+    'port').  Returns (steps_per_s, steps_timed, cores, seconds_per_step, warmups, kind, what)."""
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    if os.path.isdir(os.path.join(REF_DIR, 'dgmc')):
+        one_step, kind = _reference_step_fn(w, inputs), 'reference'
+        what = ('unmodified reference package (oracle/_ref/dgmc, sha256 %s) through the torch_geometric / '
+                'torch_scatter stand-ins of oracle/shims, __top_k__ row-chunked (matmul + topk)' %
+                open(os.path.join(REF_DIR, 'DIGEST')).read().strip()[:12])
+    else:
+        one_step, kind = _port_step_fn(w, inputs), 'port'
+        what = 'oracle port of the reference (oracle/dgmc_oracle.py: torch CPU ops, row-chunked matmul + topk)'
 
     t0 = time.perf_counter()
     one_step()  # warm-up (also sizes the sample)
@@ -160,7 +229,7 @@ def cpu_reference_steps(w, inputs, steps, warmup, budget_s):
     for _ in range(n):
         one_step()
     dt = (time.perf_counter() - t0) / n
-    return 1.0 / dt, n, cores, dt, 1 + extra
+    return 1.0 / dt, n, cores, dt, 1 + extra, kind, what
 
 
 # ------------------------------------------------------------------------------------------------
@@ -240,26 +309,45 @@ def timed_graph(fn, iters, flush):
     return max(t1 - t0, 1e-4)
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum per launch from the `ncu --set full` captures under
-# profiles/ (DBP15K shape only; None where the captured launch is not the one timed here)
-NCU_TRAFFIC_DBP15K = {
-    'K1': 19.98e6 + 47.37e6,  # topk_tc_kernel + topk_merge_kernel (r1f/r1j captures; the two cast
-                              # kernels, 40 MB fp32 in / 20 MB bf16 out, were not captured)
-    'K6': 13.08e6,            # diff_mlp_fwd_kernel<16,1> (r1f capture)
-    'K5': 15.14e6,            # balanced_lean_kernel<16>, merged pair, forward operator (r1w capture; the
-                              # transposed operator reads 34.3 MB; fix-up kernel 5.5 MB, not included)
-    'G1': 30.04e6,            # linear_tc_kernel<64,2>, 38,960 x 192 -> 64 (r1n capture: X once; y stays in L2)
-    'G2': 39.96e6,            # wgrad_tc_kernel<64> (r1n capture: G and X once; the reduce kernel not captured)
-}
+# ------------------------------------------------------------------------------------------------
+# roofline: the hot kernels timed alone, their DRAM traffic read from the committed ncu captures
+# ------------------------------------------------------------------------------------------------
+def load_ncu_traffic(tag):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch, parsed at run time from the newest
+    `profiles/*ncu_full_hot_<tag>.csv` (`ncu --set full` raw-page export of `python bench.py
+    --hot-kernels`, which launches every hot kernel once).  -> ({kernel function name: [bytes per
+    launch, in launch order]}, file name) or ({}, None) when no capture is committed."""
+    import csv
+    import glob
+    import re
+    files = sorted(glob.glob(os.path.join(ROOT, 'profiles', '*ncu_full_hot_%s.csv' % tag)))
+    if not files:
+        return {}, None
+    rows = list(csv.reader(open(files[-1])))
+    head, units = rows[0], rows[1]
+    col = {name: head.index(name) for name in ('Kernel Name', 'dram__bytes_read.sum', 'dram__bytes_write.sum')}
+    scale = {'byte': 1.0, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}
+    out = {}
+    for r in rows[2:]:
+        if len(r) <= max(col.values()):
+            continue
+        name = re.sub(r'^void\s+', '', r[col['Kernel Name']])
+        name = re.split(r'[<(]', name)[0].split('::')[-1]
+        total = sum(float(r[col[c]]) * scale[units[col[c]]] for c in ('dram__bytes_read.sum', 'dram__bytes_write.sum'))
+        out.setdefault(name, []).append(total)
+    return out, os.path.basename(files[-1])
 
 
-def kernel_rooflines(w, model, e_t, peaks, step_ms, iters=5, e_s=None):
-    """Times each hot kernel alone (cold L2) on step-shaped data.  Algorithmic bytes / flops per
-    launch follow SURVEY.md §8(d): `bytes_min` (every operand read once, every result written once)
-    when the gathered table fits in L2, else `bytes_logical` (gathered rows counted per access)."""
+def hot_kernel_cases(w, model, e_t, e_s=None, with_k1=True):
+    """The hot kernels of one training step on step-shaped data.  Each case: what to launch, how many
+    times a step launches it, its algorithmic work per launch (`bytes_min` — every
+    operand read once, every result written once — when the gathered table fits in L2, else the bytes
+    the gathers really request), and which kernel functions one launch consists of."""
     from dgmc import ops
     dev = e_t.device
     n_s, n_t, C, R, k = w['n_s'], w['n_t'], w['dim'], w['rnd_dim'], w['k']
+    n_g = n_s                         # source nodes of the graph (psi_2 runs on all of them on every rank)
+    n_s = w.get('cand_rows', n_s)     # rows of S this rank owns (row sharding): K1-K4 and K6 work on these
     k_eff = k + min(k, n_t - k)
     L, T = w['layers'], w['num_steps']
     l2 = torch.cuda.get_device_properties(dev).L2_cache_size
@@ -272,90 +360,122 @@ def kernel_rooflines(w, model, e_t, peaks, step_ms, iters=5, e_s=None):
     idx = torch.randint(n_t, (1, n_s, k_eff), generator=g).to(dev)
     cand = ops.Candidates(idx, n_t)
     cand.csr
+    nnz = n_s * k_eff
     S = torch.rand(n_s, k_eff, generator=g).to(dev)
-    r_s, p_s, p_t, x_t = rnd(n_s, R), rnd(n_s, R), rnd(n_t, R), rnd(n_t, R)
+    r_s, p_s, p_t = rnd(n_s, R), rnd(n_s, R), rnd(n_t, R)
     w2, b2 = rnd(R), torch.zeros(1, device=dev)
     # K5 as the step runs it: psi_2 aggregates on the MERGED pair (source + target graph), once per
     # layer in the forward and once (the transposed operator, same kernel) in the backward pass
     if e_s is not None:
-        e_m = torch.cat([e_s, e_t + n_s], dim=1)
-        n_m5, k5_name, k5_calls = n_s + n_t, 'merged pair', 2 * L * T
+        e_m = torch.cat([e_s, e_t + n_g], dim=1)
+        n_m, k5_name, k5_calls = n_g + n_t, 'merged pair', 2 * L * T
     else:
-        e_m, n_m5, k5_name, k5_calls = e_t, n_t, 'target graph', L * T
-    graph_t = ops.GraphCSR.of(e_m, n_m5)
-    x_m5 = rnd(n_m5, R)
+        e_m, n_m, k5_name, k5_calls = e_t, n_t, 'target graph', L * T
+    graph_m = ops.GraphCSR.of(e_m, n_m)
+    graph_m.rel
+    x_m = rnd(n_m, R)
     E = e_m.size(1)
+    cat, wl, bl = rnd(n_m, 3 * R), rnd(R, 3 * R) * 0.05, rnd(R)
+    gy = rnd(n_m, R)
+
+    def pick(table_bytes, b_min, b_gathered):
+        return (b_gathered, 'gathered') if table_bytes > l2 else (b_min, 'min')
+
+    cases = []
+
+    def add(key, name, fn, calls, work, bound, basis, kernels, graphed=False, survey_logical=None, subtract=None):
+        cases.append(dict(key=key, name=name, fn=fn, calls=calls, work=work, bound=bound, basis=basis,
+                          kernels=kernels, graphed=graphed, survey_logical=survey_logical, subtract=subtract))
+
+    if with_k1:
+        add('K1', 'K1 top-k (cast + tcgen05 GEMM/select + fp32 merge)', lambda: model.__top_k__(h_s, h_t), 1,
+            2.0 * n_s * n_t * C, 'tensor', '2*N_s*N_t*C flop', ['cast_bf16_kernel', 'topk_tc_kernel', 'topk_merge_kernel'])
+    wk, b = pick(n_t * 4 * C, (n_s + n_t) * 4 * C + 8 * nnz, 4 * C * n_s * (1 + k_eff) + 8 * nnz)
+    add('K2', 'K2 gather_dot', lambda: ops.gather_dot(h_s[0], h_t[0], cand), 1, wk, 'hbm', b, ['gather_dot_kernel'],
+        survey_logical=4 * C * n_s * (1 + k_eff) + 8 * nnz)
+    add('K3', 'K3 softmax_k fwd', lambda: ops.softmax_k(S), T + 2, 8 * nnz, 'hbm', 'min', ['softmax_k_fwd_kernel'])
+    # K4 is a by-target GATHER: per entry it reads (perm, seg, S) and one r_s row, and writes each r_t row
+    # once.  SURVEY.md §8(d)'s `logical` formula models a scatter with read-modify-write atomics
+    # (4R N_s (1 + 2 k_eff)), i.e. twice the row traffic this kernel has; it is reported beside the rate.
+    wk, b = pick(n_s * 4 * R, 8 * nnz + 4 * R * (n_s + n_t), 12 * nnz + 4 * R * nnz + 4 * R * n_t)
+    add('K4', 'K4 transport (balanced segmented gather by target)', lambda: ops.transport(S, r_s, cand), T, wk,
+        'hbm', b, ['balanced_lean_kernel', 'balanced_fixup_kernel', 'balanced_main_kernel'],
+        survey_logical=8 * nnz + 4 * R * n_s * (1 + 2 * k_eff))
+    wk, b = pick(n_m * 4 * R, 8 * n_m * R + 8 * E + 8 * n_m, 12 * n_m * R + (n_m + 2 * E) * (4 * R + 12))
+    add('K5', 'K5 rel_aggregate ([3N,N] sparse product, %s)' % k5_name, lambda: ops.rel_aggregate(x_m, graph_m),
+        k5_calls, wk, 'hbm', b, ['balanced_lean_kernel', 'balanced_fixup_kernel', 'balanced_main_kernel'],
+        survey_logical=8 * n_m * R + 2 * E * (4 * R + 4))
+    wk, b = pick(n_t * 4 * R, 4 * R * (n_s + n_t) + 12 * nnz, 4 * R * n_s * (1 + k_eff) + 12 * nnz)
+    add('K6', 'K6 diff_mlp fwd', lambda: ops.diff_mlp(S, p_s, p_t, w2, b2, cand), T, wk, 'hbm', b,
+        ['diff_mlp_fwd_kernel'], survey_logical=4 * R * n_s * (1 + k_eff) + 12 * nnz)
+    # psi_2 RelConv GEMM on the merged pair: [N_s + N_t, 3R] -> R, bias + ReLU (tcgen05 3xTF32).
+    # Bound by HBM, not by the tensor pipe: 3 x 2*N*3R*R flop is 2.9 GFLOP (2 us at peak).
+    add('G1', 'G1 linear_tc (psi_2 RelConv GEMM, %s)' % k5_name, lambda: ops.node_linear(cat, wl, bl, relu=True),
+        (L + 1) * T, 4 * n_m * (3 * R + R), 'hbm', 'min', ['linear_tc_kernel'], graphed=True)
+    # weight gradient dW [R, 3R] = G^T X over N nodes: split-K tcgen05 kernel + reduction of the partial
+    # tiles, called as the backward pass calls them (no autograd thread in between)
+    add('G2', 'G2 wgrad_tc + reduce (psi_2 RelConv weight gradient)', lambda: ops._wgrad_tc_chunked(gy, cat),
+        (L + 1) * T, 4 * n_m * (3 * R + R), 'hbm', 'min', ['wgrad_tc_kernel', 'wgrad_reduce_kernel'], graphed=True)
+    return cases
+
+
+def kernel_rooflines(w, model, e_t, peaks, step_ms, iters=5, e_s=None, traffic_tag=None, with_k1=True):
+    """Times each hot kernel alone (cold L2: a 256 MB buffer is rewritten before every launch)."""
+    dev = e_t.device
+    cases = hot_kernel_cases(w, model, e_t, e_s, with_k1)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     hbm, tf = peaks['hbm_gbs'], peaks['bf16_tflops']
+    traffic, traffic_file = load_ncu_traffic(traffic_tag) if traffic_tag else ({}, None)
+    cursor = {}   # kernel name -> launches of the capture already attributed (the capture is in case order)
     rows = []
-
-    logical = {}
-
-    def pick(table_bytes, b_min, b_logical):
-        logical['last'] = b_logical
-        return (b_logical, 'logical') if table_bytes > l2 else (b_min, 'min')
-
-    dbp15k = (n_s, n_t, C, R) == (19388, 19572, 256, 64)
-
-    def add(name, fn, calls, work, bound, basis='', graphed=False):
-        ms = timed_graph(fn, iters, flush) if graphed else timed(fn, iters, flush)
-        traffic = NCU_TRAFFIC_DBP15K.get(name[:2]) if dbp15k else None
-        achieved = work / (ms * 1e-3) / (1e12 if bound == 'tensor' else 1e9)
-        peak = tf if bound == 'tensor' else hbm
-        rows.append({'kernel': name, 'bound': bound, 'achieved': round(achieved, 2), 'peak': peak,
-                     'unit': 'TFLOP/s' if bound == 'tensor' else 'GB/s',
-                     'frac': round(achieved / peak, 4), 'traffic': traffic, 'work_basis': basis,
-                     'logical_gbs': round(logical.pop('last') / (ms * 1e-3) / 1e9, 1) if 'last' in logical else None,
-                     'ms_per_launch': round(ms, 4), 'launches_per_step': calls,
-                     'share_of_step': round(ms * calls / step_ms, 4) if step_ms else None})
-
-    with torch.no_grad():
-        add('K1 top-k (cast + tcgen05 GEMM/select + fp32 merge)', lambda: model.__top_k__(h_s, h_t), 1,
-            2.0 * n_s * n_t * C, 'tensor', '2*N_s*N_t*C flop')
-        wk, b = pick(n_t * 4 * C, (n_s + n_t) * 4 * C + 8 * n_s * k_eff,
-                     4 * C * n_s * (1 + k_eff) + 8 * n_s * k_eff)
-        add('K2 gather_dot', lambda: ops.gather_dot(h_s[0], h_t[0], cand), 1, wk, 'hbm', b)
-        add('K3 softmax_k fwd', lambda: ops.softmax_k(S), T + 2, 8 * n_s * k_eff, 'hbm', 'min')
-        wk, b = pick(n_s * 4 * R, 8 * n_s * k_eff + 4 * R * (n_s + n_t),
-                     8 * n_s * k_eff + 4 * R * n_s * (1 + 2 * k_eff))
-        add('K4 transport (balanced segmented gather by target)', lambda: ops.transport(S, r_s, cand), T,
-            wk, 'hbm', b)
-        wk, b = pick(n_m5 * 4 * R, 8 * n_m5 * R + 8 * E + 8 * n_m5, 8 * n_m5 * R + 2 * E * (4 * R + 4))
-        add('K5 rel_aggregate ([3N,N] sparse product, %s)' % k5_name,
-            lambda: ops.rel_aggregate(x_m5, graph_t), k5_calls, wk, 'hbm', b)
-        wk, b = pick(n_t * 4 * R, 4 * R * (n_s + n_t) + 12 * n_s * k_eff,
-                     4 * R * n_s * (1 + k_eff) + 12 * n_s * k_eff)
-        add('K6 diff_mlp fwd', lambda: ops.diff_mlp(S, p_s, p_t, w2, b2, cand), T, wk, 'hbm', b)
-        # psi_2 RelConv GEMM on the merged pair: [N_s + N_t, 3R] -> R, bias + ReLU (tcgen05 3xTF32).
-        # Bound by HBM, not by the tensor pipe: 3 x 2*N*3R*R flop is 2.9 GFLOP (2 us at peak).
-        n_m = n_s + n_t
-        cat, wl, bl = rnd(n_m, 3 * R), rnd(R, 3 * R) * 0.05, rnd(R)
-        add('G1 linear_tc (psi_2 RelConv GEMM, merged pair)',
-            lambda: ops.node_linear(cat, wl, bl, relu=True), (L + 1) * T, 4 * n_m * (3 * R + R), 'hbm', 'min',
-            graphed=True)
-    gy = rnd(n_m, R)
-    cat.requires_grad_(False)
-    wl.requires_grad_(True)
-
-    def wgrad_once():
-        wl.grad = None
-        y = ops.node_linear(cat, wl)
-        y.backward(gy)
-    with torch.enable_grad():
-        # weight gradient dW [R, 3R] = G^T X over N nodes (split-K tcgen05 + reduce); the timed call
-        # includes the forward GEMM above, which is subtracted
-        t_pair = timed_graph(wgrad_once, iters, flush)
-    with torch.no_grad():
-        t_fwd = timed_graph(lambda: ops.node_linear(cat, wl), iters, flush)
-    ms = max(t_pair - t_fwd, 1e-4)
-    work = 4 * n_m * (3 * R + R)
-    rows.append({'kernel': 'G2 wgrad_tc + reduce (psi_2 RelConv weight gradient)', 'bound': 'hbm',
-                 'achieved': round(work / (ms * 1e-3) / 1e9, 2), 'peak': hbm, 'unit': 'GB/s',
-                 'frac': round(work / (ms * 1e-3) / 1e9 / hbm, 4),
-                 'traffic': NCU_TRAFFIC_DBP15K.get('G2') if dbp15k else None, 'work_basis': 'min',
-                 'logical_gbs': None, 'ms_per_launch': round(ms, 4), 'launches_per_step': (L + 1) * T,
-                 'share_of_step': round(ms * (L + 1) * T / step_ms, 4) if step_ms else None})
+    for c in cases:
+        with torch.no_grad():
+            ms = timed_graph(c['fn'], iters, flush) if c['graphed'] else timed(c['fn'], 1 if c['key'] == 'K1' and iters < 3 else iters, flush)
+            if c['subtract'] is not None:
+                ms = max(ms - timed_graph(c['subtract'], iters, flush), 1e-4)
+        t_bytes, found = 0.0, False
+        for kn in c['kernels']:
+            if kn in traffic:
+                i = cursor.get(kn, 0)
+                n_launch = 2 if kn == 'cast_bf16_kernel' else 1
+                vals = traffic[kn][i:i + n_launch]
+                if vals:
+                    t_bytes += sum(vals)
+                    found = True
+                    cursor[kn] = i + n_launch
+        achieved = c['work'] / (ms * 1e-3) / (1e12 if c['bound'] == 'tensor' else 1e9)
+        peak = tf if c['bound'] == 'tensor' else hbm
+        rows.append({'kernel': c['name'], 'bound': c['bound'], 'achieved': round(achieved, 2), 'peak': peak,
+                     'unit': 'TFLOP/s' if c['bound'] == 'tensor' else 'GB/s', 'frac': round(achieved / peak, 4),
+                     'traffic': t_bytes if found else None, 'traffic_source': traffic_file if found else None,
+                     'work_basis': c['basis'], 'work_per_launch': c['work'],
+                     'survey_logical_gbs': round(c['survey_logical'] / (ms * 1e-3) / 1e9, 1) if c['survey_logical'] else None,
+                     'ms_per_launch': round(ms, 4), 'launches_per_step': c['calls'],
+                     'share_of_step': round(ms * c['calls'] / step_ms, 4) if step_ms else None})
     return rows
+
+
+def run_hot_kernels(w, dev, tag, with_k1):
+    """`--hot-kernels`: every hot kernel once (after one warm-up launch each) inside the NVTX range
+    "hot", for `ncu --set full --nvtx --nvtx-include "hot/"`; the raw-page CSV export of that capture,
+    committed as profiles/<round>_ncu_full_hot_<tag>.csv, is what `roofline*.traffic` is read from."""
+    from dgmc.models import DGMC, RelCNN
+    g = torch.Generator().manual_seed(11)
+    e_s = torch.randint(w['n_s'], (2, w['e_s']), generator=g).to(dev)
+    e_t = torch.randint(w['n_t'], (2, w['e_t']), generator=g).to(dev)
+    model = DGMC(RelCNN(8, 8, 1), RelCNN(w['rnd_dim'], w['rnd_dim'], 1), num_steps=w['num_steps'], k=w['k']).to(dev)
+    cases = hot_kernel_cases(w, model, e_t, e_s, with_k1)
+    with torch.no_grad():
+        for c in cases:
+            c['fn']()
+    torch.cuda.synchronize()
+    torch.cuda.nvtx.range_push('hot')
+    with torch.no_grad():
+        for c in cases:
+            c['fn']()
+    torch.cuda.synchronize()
+    torch.cuda.nvtx.range_pop()
+    emit({'hot_kernels': [c['key'] for c in cases], 'tag': tag})
 
 
 def pascal_step_bench(dev, steps, warmup):
@@ -421,18 +541,74 @@ def pascal_step_bench(dev, steps, warmup):
                             'the reference scripts, so no graph capture)'}})
 
 
-def scale_kernels(n, dev):
-    """`--scale-kernels N`: the hot kernels alone on an N x N-node synthetic pair (BASELINE.json
-    configs[4] shape at N = 1,000,000: 256-d embeddings, R = 64, k_eff = 20, 5 out-edges per node),
-    where the gathered tables no longer fit in L2 and HBM is the roofline."""
+def scale_workload(n):
+    """BASELINE.json configs[4] shape: an N x N-node pair, 256-d embeddings, R = 64, k = 10 (k_eff = 20),
+    5 out-edges per node — where the gathered tables no longer fit in L2 and HBM is the roofline."""
+    return dict(n_s=n, n_t=n, dim=256, rnd_dim=64, k=10, layers=3, num_steps=10, e_s=5 * n, e_t=5 * n)
+
+
+def scale_rooflines(n, dev, iters=3):
     from dgmc.models import DGMC, RelCNN
-    w = dict(n_s=n, n_t=n, dim=256, rnd_dim=64, k=10, layers=3, num_steps=10)
+    w = scale_workload(n)
     g = torch.Generator().manual_seed(11)
+    e_s = torch.randint(n, (2, 5 * n), generator=g).to(dev)
     e_t = torch.randint(n, (2, 5 * n), generator=g).to(dev)
     model = DGMC(RelCNN(8, 8, 1), RelCNN(64, 64, 1), num_steps=10, k=10).to(dev)
-    rows = kernel_rooflines(w, model, e_t, load_peaks(), None, iters=3)
+    tag = '1m' if n == 1000000 else None
+    return kernel_rooflines(w, model, e_t, load_peaks(), None, iters=iters, e_s=e_s, traffic_tag=tag)
+
+
+def scale_kernels(n, dev):
+    """`--scale-kernels N`: the hot kernels alone on an N x N-node synthetic pair."""
     emit({'scale_kernels': {'n_s': n, 'n_t': n, 'C': 256, 'R': 64, 'k_eff': 20, 'edges': 5 * n},
-          'roofline_all': rows})
+          'roofline_all': scale_rooflines(n, dev)})
+
+
+def sharded_parity(model, w, d, dev, rank, world):
+    """Multi-GPU parity inside the run the driver sees: one un-graphed training-mode forward of the
+    row-sharded model on all ranks and the same forward of the single-GPU model (same weights, same
+    seed -> same dropout masks, negatives and indicators) on rank 0; the ranks' rows of S_L are gathered
+    and compared.  Candidate lists must be identical; values agree up to the summation order of the
+    r_t all-reduce (tolerance 1e-4 relative at this shape, see tests/test_gpu_bench_configs.py)."""
+    import torch.distributed as dist
+    from dgmc.models import DGMC
+    from dgmc.models.sharded import row_block
+    seed = 4321
+    with torch.no_grad():
+        torch.manual_seed(seed)
+        _, S_sh = model(d['x_s'], d['e_s'], None, None, d['x_t'], d['e_t'], None, None, d['y'])
+        share = model.loss(S_sh, d['y'])
+        loss_sh = model.global_loss(share).item()
+    n_s, k_eff = w['n_s'], S_sh.__idx__.size(1)
+    rows_max = max(row_block(n_s, q, world)[1] - row_block(n_s, q, world)[0] for q in range(world))
+    pad_v = torch.zeros(rows_max, k_eff, device=dev)
+    pad_i = torch.full((rows_max, k_eff), -1, dtype=torch.long, device=dev)
+    pad_v[:S_sh.__val__.size(0)] = S_sh.__val__
+    pad_i[:S_sh.__idx__.size(0)] = S_sh.__idx__
+    all_v = [torch.empty_like(pad_v) for _ in range(world)]
+    all_i = [torch.empty_like(pad_i) for _ in range(world)]
+    dist.all_gather(all_v, pad_v)
+    dist.all_gather(all_i, pad_i)
+    result = None
+    if rank == 0:
+        val = torch.cat([all_v[q][:row_block(n_s, q, world)[1] - row_block(n_s, q, world)[0]] for q in range(world)])
+        idx = torch.cat([all_i[q][:row_block(n_s, q, world)[1] - row_block(n_s, q, world)[0]] for q in range(world)])
+        single = DGMC(model.psi_1, model.psi_2, num_steps=model.num_steps, k=model.k, detach=model.detach)
+        single.mlp = model.mlp
+        single.train(model.training)
+        with torch.no_grad():
+            torch.manual_seed(seed)
+            _, S_1 = single(d['x_s'], d['e_s'], None, None, d['x_t'], d['e_t'], None, None, d['y'])
+            loss_1 = single.loss(S_1, d['y']).item()
+        ref = S_1.__val__
+        rel = ((val - ref).abs() / ref.abs().clamp_min(1e-6)).max().item()
+        result = {'checked': True, 'idx_equal': bool(torch.equal(idx, S_1.__idx__)), 'max_rel_err': rel,
+                  'loss_rel_err': abs(loss_sh - loss_1) / max(abs(loss_1), 1e-12), 'tolerance': 1e-4,
+                  'what': 'S_L rows of all ranks (training-mode forward, shared seed) against the '
+                          'single-GPU model on rank 0'}
+        result['ok'] = result['idx_equal'] and rel <= 1e-4 and result['loss_rel_err'] <= 1e-4
+    dist.barrier()
+    return result
 
 
 def stage(msg):
@@ -465,6 +641,10 @@ def main():
     ap.add_argument('--pascal', action='store_true', help='time the PascalVOC-shaped dense config and exit')
     ap.add_argument('--scale-kernels', type=int, default=0, metavar='N',
                     help='time the hot kernels alone on an N x N-node pair and exit')
+    ap.add_argument('--hot-kernels', action='store_true',
+                    help='launch every hot kernel once inside the NVTX range "hot" and exit (for ncu --set full '
+                         '--nvtx --nvtx-include "hot/"); with --scale-kernels N on the N x N pair')
+    ap.add_argument('--no-roofline-1m', action='store_true', help='skip the 1M x 1M kernel sweep of the N=1 line')
     ap.add_argument('--profile-eager', action='store_true',
                     help='warm up, run --steps eager steps inside the NVTX range "timed_step" and exit '
                          '(for ncu --nvtx --nvtx-include "timed_step/")')
@@ -493,15 +673,14 @@ def main():
             return 0
         inputs = make_inputs(w)
         budget = args.cpu_budget or 150.0
-        sps, n, cores, dt, wu = cpu_reference_steps(w, inputs, args.steps, args.warmup, budget)
-        sample = ('%d full steps of the same workload (oracle port of the reference: torch CPU '
-                  'ops, row-chunked matmul+topk for __top_k__), %d threads' % (n, cores))
+        sps, n, cores, dt, wu, kind, what = cpu_reference_steps(w, inputs, args.steps, args.warmup, budget)
+        sample = '%d full steps of the same workload: %s; %d threads' % (n, what, cores)
         emit({
             'impl': 'reference', 'metric': METRIC, 'value': sps, 'unit': 'steps/s', 'n_gpus': 0,
             'steps': n, 'warmup': wu, 'ms_per_step': dt * 1e3, 'higher_is_better': True,
-            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'scaling': 'strong', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
             'config': config,
-            'cpu_baseline': {'value': sps, 'unit': 'steps/s', 'cores': cores, 'kind': 'port',
+            'cpu_baseline': {'value': sps, 'unit': 'steps/s', 'cores': cores, 'kind': kind,
                              'sample': sample},
             'e2e': {'value': sps, 'unit': 'steps/s', 'h2d_bytes_per_step': 0,
                     'd2h_bytes_per_step': 0}})
@@ -510,6 +689,12 @@ def main():
     import torch.distributed as dist
     torch.cuda.set_device(local)
     dev = torch.device('cuda', local)
+    if args.hot_kernels:
+        if args.scale_kernels:
+            run_hot_kernels(scale_workload(args.scale_kernels), dev, '%d' % args.scale_kernels, with_k1=False)
+        else:
+            run_hot_kernels(w, dev, 'dbp15k', with_k1=True)
+        return 0
     if args.scale_kernels:
         scale_kernels(args.scale_kernels, dev)
         return 0
@@ -544,6 +729,9 @@ def main():
         torch.cuda.nvtx.range_pop()
         emit({'profile_eager_steps': args.steps})
         return 0
+
+    parity = sharded_parity(model, w, d, dev, rank, world) if world > 1 else None
+    torch.manual_seed(1234)
 
     from dgmc.utils import GraphedTrainStep
     args_of = lambda t: (t['x_s'], t['e_s'], None, None, t['x_t'], t['e_t'], None, None, t['y'])  # noqa: E731
@@ -658,14 +846,21 @@ def main():
     out = None
     if rank == 0:
         peaks = load_peaks()
-        rl = kernel_rooflines(w, model, d['e_t'], peaks, ms_per_step, e_s=d['e_s'])
+        w_rl = dict(w)
+        if world > 1:   # rank 0's share of the rows of S; psi_2 (K5, G1, G2) is replicated on the whole pair
+            from dgmc.models.sharded import row_block
+            lo, hi = row_block(w['n_s'], 0, world)
+            w_rl['cand_rows'] = hi - lo
+        rl = kernel_rooflines(w_rl, model, d['e_t'], peaks, ms_per_step, e_s=d['e_s'],
+                              traffic_tag='dbp15k' if (not args.nodes and world == 1 and not args.k) else None)
         top = max(rl, key=lambda r: r['share_of_step'])
-        roofline = {k_: top[k_] for k_ in ('bound', 'achieved', 'peak', 'unit', 'frac', 'traffic')}
+        roofline = {k_: top[k_] for k_ in ('bound', 'achieved', 'peak', 'unit', 'frac', 'traffic', 'traffic_source')}
         roofline.update(kernel=top['kernel'], peak_source=peaks['source'] + ' (burst: kernel timed alone)')
         out = {
             'metric': METRIC, 'value': value, 'unit': 'steps/s', 'n_gpus': world, 'steps': args.steps,
             'warmup': args.warmup, 'ms_per_step': ms_per_step, 'higher_is_better': True,
-            'scaling': 'strong' if world > 1 else 'weak', 'vs_baseline': None, 'dtype': 'f32',
+            # one job = one graph pair whatever N is: its source rows are divided over the GPUs
+            'scaling': 'strong', 'vs_baseline': None, 'dtype': 'f32',
             'data': 'synthetic',
             'config': dict(config, parallelism=('source rows sharded over %d GPUs, r_t all-reduce per consensus step '
                                         '(NCCL), psi replicated' % world) if world > 1 else 'single GPU',
@@ -681,13 +876,28 @@ def main():
             'eager_ms_per_step': eager_ms,
             'roofline': roofline, 'roofline_all': rl,
         }
+        if parity is not None:
+            out['parity'] = parity
+        if world == 1 and not args.nodes and not args.k and not args.no_roofline_1m:
+            # BASELINE.json configs[4] shape, kernels alone: where HBM, not latency, is the roofline
+            del model, graphed, e2e_step
+            ops_mod = sys.modules['dgmc.ops']
+            ops_mod.clear_caches()
+            torch.cuda.empty_cache()
+            out['roofline_1m'] = {'shape': '1,000,000 x 1,000,000 nodes, C=256, R=64, k_eff=20, 5 M edges per graph; '
+                                           'kernels timed alone, cold L2',
+                                  'kernels': scale_rooflines(1000000, dev, iters=2)}
         if world == 1 and not args.no_cpu_baseline and not args.nodes and not args.k:
-            sps, n, cores, dt, _ = cpu_reference_steps(w, host, 2, 1, args.cpu_budget or 30.0)
+            sps, n, cores, dt, _, kind, what = cpu_reference_steps(w, host, 2, 1, args.cpu_budget or 30.0)
             out['cpu_baseline'] = {
-                'value': sps, 'unit': 'steps/s', 'cores': cores, 'kind': 'port',
-                'sample': '%d full step(s) of the same workload after 1 warm-up, oracle port of the '
-                          'reference (torch CPU, chunked matmul+topk), %.1f s/step' % (n, dt)}
+                'value': sps, 'unit': 'steps/s', 'cores': cores, 'kind': kind,
+                'sample': '%d full step(s) of the same workload after 1 warm-up: %s; %.1f s/step' % (n, what, dt)}
         emit(out)
+    if world > 1 and rank == 0 and parity is not None and not parity['ok']:
+        print('bench: multi-GPU parity check FAILED: %s' % parity, file=sys.stderr, flush=True)
+        store.set('dgmc_bench_done', '1')
+        time.sleep(1.0)
+        os._exit(3)
     if world > 1:
         store.set('dgmc_bench_done', '1')
         sys.stderr.flush()

@@ -37,6 +37,17 @@ inline int sm_count() {
     return cached;
 }
 
+// cuTensorMapEncodeTiled is a DRIVER call and needs a current context on the calling thread.  A thread
+// that has not yet made a runtime call that binds the primary context (e.g. PyTorch's autograd worker
+// running the first backward pass of the process) has none: bind it once per thread.
+inline void ensure_context() {
+    static thread_local bool bound = false;
+    if (!bound) {
+        cudaFree(nullptr);
+        bound = true;
+    }
+}
+
 // grid for a grid-stride kernel: a whole number of waves of `per_sm` resident CTAs per SM
 inline int wave_grid(long long work_items, int items_per_block, int per_sm) {
     long long need = (work_items + items_per_block - 1) / items_per_block;

@@ -445,6 +445,7 @@ static EncodeTiledFnR rc_encode_tiled() {
 static int rc_make_map(CUtensorMap* map, const void* base, long long rows, long long cols, long long ld,
                        int box_rows) {
     memset(map, 0, sizeof(*map));
+    ensure_context();
     EncodeTiledFnR enc = rc_encode_tiled();
     if (!enc) { set_error("relconv_tc: cuTensorMapEncodeTiled not available from the driver"); return DGMC_ERR_CUDA; }
     const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};

@@ -379,6 +379,7 @@ static EncodeTiledFn encode_tiled() {
 }
 
 static int make_map(CUtensorMap* map, const void* base, long long rows, int c_pad) {
+    ensure_context();
     EncodeTiledFn enc = encode_tiled();
     if (!enc) { set_error("topk_tc: cuTensorMapEncodeTiled not available from the driver"); return DGMC_ERR_CUDA; }
     const cuuint64_t dims[2] = {(cuuint64_t)c_pad, (cuuint64_t)rows};

@@ -260,6 +260,7 @@ static EncodeTiledFnW wt_encode_tiled() {
 
 // fp32 [rows(k) x cols(channels)] row-major, pitch ld floats; box = 32 channels x 32 k rows
 static int wt_make_map(CUtensorMap* map, const void* base, long long rows, long long cols, long long ld) {
+    ensure_context();
     EncodeTiledFnW enc = wt_encode_tiled();
     if (!enc) { set_error("wgrad_tc: cuTensorMapEncodeTiled not available from the driver"); return DGMC_ERR_CUDA; }
     memset(map, 0, sizeof(*map));
