@@ -1,0 +1,243 @@
+// Collectives of the row-sharded path over NVLink peer memory (one process per GPU, one node).
+//
+// The reference is single-process; the sharded path (dgmc/models/sharded.py) needs, per
+// consensus step, the sum over ranks of the partial indicator transport r_t [N_t, R] (dgmc.py:209-212 is
+// a sum over SOURCE rows, which are sharded) and, for node-sharded psi_2, an all-gather of a layer's
+// features / a reduce-scatter of their gradients.  At the DBP15K shape these are 1-10 MB messages, 100
+// of them per training step: latency, not bandwidth.  NCCL's ring costs ~38 us per 5 MB all-reduce
+// here; the kernels below take ~10 us because every rank reads / writes its peers' buffers DIRECTLY
+// (plain ld / st through the NVLink peer mapping of a symmetric allocation: same offset, every rank),
+// synchronising with flag words in the same allocation:
+//
+//   all-reduce      two-shot: rank r sums slice r of all ranks' partials (fixed rank order, so every
+//                   rank ends up with bit-identical sums) and stores the result into every rank's output
+//   all-gather      each rank stores its block into every rank's output
+//   reduce-scatter  each rank sums its block over all ranks' inputs
+//
+// Synchronisation is per thread block: block b of the kernel handshakes with block b of every peer
+// (a release-store of the block's call count into the peer's flag word [b][my rank], then polling the
+// local words [b][peer]: one NVLink crossing, no round trip).  A block starts to touch peer memory only
+// after every peer's block b has started, i.e. after everything earlier in that peer's stream has
+// finished, and — where the caller asks for the closing handshake — leaves only after every peer's
+// block b has finished touching it.  Spins give up after ~2 s and raise a device flag
+// (dgmc_sym_timeouts) instead of hanging the GPU.
+//
+// These entry points read and write ONLY what the caller passes: the table of the ranks' base pointers
+// of one symmetric allocation (e.g. torch.distributed._symmetric_memory: handle.buffer_ptrs_dev) and
+// byte offsets inside it.  Nothing here uses TMA.
+#include "common.cuh"
+#include "../../include/dgmc_b200.h"
+
+namespace dgmc {
+
+constexpr int SYM_THREADS = 512;
+constexpr int SYM_MAX_BLOCKS = DGMC_SYM_MAX_BLOCKS;
+constexpr int SYM_MAX_WORLD = DGMC_SYM_MAX_WORLD;
+constexpr long long SYM_TIMEOUT_CYCLES = 4000000000LL;   // ~2 s at 1.9 GHz
+
+__device__ int g_sym_timeouts = 0;
+
+struct SymPeers {
+    unsigned char* base[SYM_MAX_WORLD];
+};
+
+// flag words of one rank: [phase 0/1][block][sender rank], then this rank's own call counters
+// [phase][block] (never touched by peers)
+__device__ __forceinline__ unsigned* sym_flag(const SymPeers& p, int owner, long long pad_off, int phase,
+                                              int block, int from) {
+    return reinterpret_cast<unsigned*>(p.base[owner] + pad_off) +
+           ((size_t)phase * SYM_MAX_BLOCKS + block) * SYM_MAX_WORLD + from;
+}
+__device__ __forceinline__ unsigned* sym_epoch(const SymPeers& p, int rank, long long pad_off, int phase, int block) {
+    return reinterpret_cast<unsigned*>(p.base[rank] + pad_off) + (size_t)2 * SYM_MAX_BLOCKS * SYM_MAX_WORLD +
+           (size_t)phase * SYM_MAX_BLOCKS + block;
+}
+
+// Block-wise handshake with the same block of every peer: ONE-WAY.  Each side keeps a call counter
+// per (phase, block); arriving = a release-store of the new count into every peer's flag word (no
+// round trip over NVLink), waiting = polling the local flag words until every peer's count has
+// caught up.  Counters only grow, so the words never need resetting.
+__device__ __forceinline__ void sym_block_barrier(const SymPeers& p, long long pad_off, int phase, int rank,
+                                                  int world) {
+    __syncthreads();          // the block's stores so far happen-before the release below (cumulativity)
+    if ((int)threadIdx.x < world) {
+        const int peer = threadIdx.x;
+        unsigned* ep = sym_epoch(p, rank, pad_off, phase, blockIdx.x);
+        const unsigned target = *reinterpret_cast<volatile unsigned*>(ep) + 1u;
+        if (peer != rank) {
+            unsigned* theirs = sym_flag(p, peer, pad_off, phase, blockIdx.x, rank);
+            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(theirs), "r"(target) : "memory");
+            const unsigned* mine = sym_flag(p, rank, pad_off, phase, blockIdx.x, peer);
+            const long long t0 = clock64();
+            unsigned seen;
+            do {    // relaxed polling, one acquire fence once the peer's count has arrived
+                asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(mine) : "memory");
+                if ((int)(seen - target) >= 0) break;
+                if (clock64() - t0 > SYM_TIMEOUT_CYCLES) { atomicAdd(&g_sym_timeouts, 1); break; }
+            } while (true);
+            asm volatile("fence.acquire.sys;" ::: "memory");
+        }
+        __syncwarp((1u << world) - 1u);
+        if (peer == rank) *reinterpret_cast<volatile unsigned*>(ep) = target;
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ float4 add4(float4 a, const float4 b) {
+    a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+    return a;
+}
+
+// out_r[i] = sum_p in_p[i] on every rank r; n4 float4 elements.  mc != nullptr: the allocation's
+// multicast mapping (NVLink SHARP): one multimem.ld_reduce makes the SWITCH add the ranks' copies of an
+// element and one multimem.st writes the sum into every rank's output — per rank n / world elements in
+// and out instead of (world - 1) / world * n each way through SM loads.
+__global__ void __launch_bounds__(SYM_THREADS) sym_all_reduce_kernel(const SymPeers p, unsigned char* mc, int rank,
+                                                                     int world, long long in_off, long long out_off,
+                                                                     long long pad_off, long long n4) {
+    sym_block_barrier(p, pad_off, 0, rank, world);       // every rank's partial is complete
+    const long long lo = n4 * rank / world, hi = n4 * (rank + 1) / world;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    if (mc) {
+        const float4* src = reinterpret_cast<const float4*>(mc + in_off);
+        float4* dst = reinterpret_cast<float4*>(mc + out_off);
+        for (long long i = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += stride) {
+            float4 v;
+            asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                         : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(src + i) : "memory");
+            asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+                         ::"l"(dst + i), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+        }
+    } else {
+        // four elements per thread and round: all peer loads of a round are in flight together
+        for (long long i0 = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < hi; i0 += 4 * stride) {
+            float4 acc[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const long long i = i0 + u * stride;
+                if (i < hi) {
+                    acc[u] = __ldcg(reinterpret_cast<const float4*>(p.base[0] + in_off) + i);
+                    for (int q = 1; q < world; ++q)
+                        acc[u] = add4(acc[u], __ldcg(reinterpret_cast<const float4*>(p.base[q] + in_off) + i));
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const long long i = i0 + u * stride;
+                if (i < hi)
+                    for (int q = 0; q < world; ++q)
+                        __stcg(reinterpret_cast<float4*>(p.base[q] + out_off) + i, acc[u]);
+            }
+        }
+    }
+    sym_block_barrier(p, pad_off, 1, rank, world);       // every rank's slice has landed everywhere
+}
+
+// out_r[rank * block4 + i] = in[i] on every rank r
+__global__ void __launch_bounds__(SYM_THREADS) sym_all_gather_kernel(const SymPeers p, int rank, int world,
+                                                                     const float4* __restrict__ in,
+                                                                     long long out_off, long long pad_off,
+                                                                     long long block4, int sync_before) {
+    // the opening handshake (peers have let go of the output region) is not needed when the caller
+    // alternates between two output regions: see dgmc_b200.h
+    if (sync_before) sym_block_barrier(p, pad_off, 0, rank, world);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < block4;
+         i += (long long)gridDim.x * blockDim.x) {
+        const float4 v = in[i];
+        for (int q = 0; q < world; ++q)
+            __stcg(reinterpret_cast<float4*>(p.base[q] + out_off) + (long long)rank * block4 + i, v);
+    }
+    sym_block_barrier(p, pad_off, 1, rank, world);
+}
+
+// out[i] = sum_p in_p[rank * block4 + i]
+__global__ void __launch_bounds__(SYM_THREADS) sym_reduce_scatter_kernel(const SymPeers p, int rank, int world,
+                                                                         long long in_off, float4* __restrict__ out,
+                                                                         long long pad_off, long long block4,
+                                                                         int sync_after) {
+    sym_block_barrier(p, pad_off, 0, rank, world);       // every rank's input is complete
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < block4;
+         i += (long long)gridDim.x * blockDim.x) {
+        const long long j = (long long)rank * block4 + i;
+        float4 acc = __ldcg(reinterpret_cast<const float4*>(p.base[0] + in_off) + j);
+        for (int q = 1; q < world; ++q)
+            acc = add4(acc, __ldcg(reinterpret_cast<const float4*>(p.base[q] + in_off) + j));
+        out[i] = acc;
+    }
+    // closing handshake (peers have finished reading this rank's input): not needed when the caller
+    // alternates between two input regions
+    if (sync_after) sym_block_barrier(p, pad_off, 1, rank, world);
+}
+
+static int sym_peers(SymPeers* p, const void* const* bases, int rank, int world, const char* what) {
+    if (!bases || world < 1 || world > SYM_MAX_WORLD || rank < 0 || rank >= world) {
+        set_error("%s: bad rank / world (%d / %d; at most %d ranks)", what, rank, world, SYM_MAX_WORLD);
+        return DGMC_ERR_INVALID;
+    }
+    for (int q = 0; q < SYM_MAX_WORLD; ++q)
+        p->base[q] = q < world ? static_cast<unsigned char*>(const_cast<void*>(bases[q])) : nullptr;
+    for (int q = 0; q < world; ++q)
+        if (!p->base[q]) { set_error("%s: null base pointer for rank %d", what, q); return DGMC_ERR_INVALID; }
+    return DGMC_OK;
+}
+
+// whole CTAs only where there is work, never more than the flag array holds
+static int sym_grid(long long items) {
+    long long need = (items + SYM_THREADS - 1) / SYM_THREADS;
+    if (need < 1) need = 1;
+    const long long cap = sm_count() < SYM_MAX_BLOCKS ? sm_count() : SYM_MAX_BLOCKS;
+    return (int)(need < cap ? need : cap);
+}
+
+}  // namespace dgmc
+
+using namespace dgmc;
+
+extern "C" size_t dgmc_sym_pad_bytes(void) {
+    return ((size_t)2 * SYM_MAX_BLOCKS * SYM_MAX_WORLD + 2 * SYM_MAX_BLOCKS) * sizeof(unsigned);
+}
+
+extern "C" int dgmc_sym_all_reduce(const void* const* peer_bases, const void* multicast_base, int rank, int world,
+                                   int64_t in_off, int64_t out_off, int64_t pad_off, int64_t n,
+                                   dgmc_stream_t stream) {
+    SymPeers p;
+    if (int e = sym_peers(&p, peer_bases, rank, world, "sym_all_reduce")) return e;
+    DGMC_REQUIRE(n >= 0 && n % 4 == 0 && in_off % 16 == 0 && out_off % 16 == 0 && pad_off % 4 == 0,
+                 "sym_all_reduce: n must be a multiple of 4 floats, offsets 16-byte aligned");
+    const long long n4 = n / 4;
+    sym_all_reduce_kernel<<<sym_grid((n4 + world - 1) / world), SYM_THREADS, 0, stream>>>(
+        p, static_cast<unsigned char*>(const_cast<void*>(multicast_base)), rank, world, in_off, out_off, pad_off, n4);
+    return check_launch("sym_all_reduce");
+}
+
+extern "C" int dgmc_sym_all_gather(const void* const* peer_bases, int rank, int world, const float* in,
+                                   int64_t out_off, int64_t pad_off, int64_t block, int sync_before,
+                                   dgmc_stream_t stream) {
+    SymPeers p;
+    if (int e = sym_peers(&p, peer_bases, rank, world, "sym_all_gather")) return e;
+    DGMC_REQUIRE(in && block >= 0 && block % 4 == 0 && out_off % 16 == 0 && pad_off % 4 == 0 &&
+                     (reinterpret_cast<uintptr_t>(in) & 15) == 0,
+                 "sym_all_gather: block must be a multiple of 4 floats, pointers / offsets 16-byte aligned");
+    sym_all_gather_kernel<<<sym_grid(block / 4), SYM_THREADS, 0, stream>>>(
+        p, rank, world, reinterpret_cast<const float4*>(in), out_off, pad_off, block / 4, sync_before);
+    return check_launch("sym_all_gather");
+}
+
+extern "C" int dgmc_sym_reduce_scatter(const void* const* peer_bases, int rank, int world, int64_t in_off,
+                                       float* out, int64_t pad_off, int64_t block, int sync_after,
+                                       dgmc_stream_t stream) {
+    SymPeers p;
+    if (int e = sym_peers(&p, peer_bases, rank, world, "sym_reduce_scatter")) return e;
+    DGMC_REQUIRE(out && block >= 0 && block % 4 == 0 && in_off % 16 == 0 && pad_off % 4 == 0 &&
+                     (reinterpret_cast<uintptr_t>(out) & 15) == 0,
+                 "sym_reduce_scatter: block must be a multiple of 4 floats, pointers / offsets 16-byte aligned");
+    sym_reduce_scatter_kernel<<<sym_grid(block / 4), SYM_THREADS, 0, stream>>>(
+        p, rank, world, in_off, reinterpret_cast<float4*>(out), pad_off, block / 4, sync_after);
+    return check_launch("sym_reduce_scatter");
+}
+
+extern "C" int dgmc_sym_timeouts(void) {
+    int v = 0;
+    if (cudaMemcpyFromSymbol(&v, g_sym_timeouts, sizeof(int)) != cudaSuccess) return -1;
+    return v;
+}

@@ -275,6 +275,40 @@ int dgmc_dense_consensus_bwd(const float* g, const float* ps, const float* pt, c
                              float* d_w2, float* d_b2, int B, int n_s, int n_t, int r,
                              void* workspace, size_t workspace_bytes, dgmc_stream_t stream);
 
+/* ---- multi-GPU: collectives of the row-sharded path over NVLink peer memory ---------------------
+ * No counterpart in the reference (single process).  One process per GPU; the ranks share ONE symmetric
+ * allocation (same size and layout on every rank, every rank's copy mapped into every process, e.g.
+ * torch.distributed._symmetric_memory).  peer_bases: HOST array of `world` device pointers, entry q =
+ * base of rank q's copy as mapped in THIS process; *_off: byte offsets inside the allocation, equal on
+ * all ranks.  pad_off: dgmc_sym_pad_bytes() bytes of flag words, zeroed once before the first call.
+ * Every rank must issue the same calls in the same order (they handshake block by block; a rank that
+ * waits ~2 s gives up and counts a timeout instead of hanging, see dgmc_sym_timeouts()).  At most
+ * DGMC_SYM_MAX_WORLD ranks.  Sums are taken in rank order 0, 1, ... by exactly one rank per element, so
+ * all ranks receive bit-identical results.
+ *   all_reduce:      out_r[0:n] = sum_q in_q[0:n] on every rank r            (the r_t all-reduce)
+ *   all_gather:      out_r[rank*block : (rank+1)*block] = in (local pointer)  (layer features of psi_2 / o_t)
+ *   reduce_scatter:  out (local pointer) [0:block] = sum_q in_q[rank*block : (rank+1)*block]
+ * n and block in floats, multiples of 4.  multicast_base (nullable): the allocation's NVLink-SHARP
+ * multicast mapping, if the fabric has one — the switch then does the additions (multimem.ld_reduce)
+ * and the broadcast (multimem.st).
+ * Handshakes: all_reduce opens ("all partials complete") and closes ("all results landed") with one.
+ * all_gather always closes with one; its opening one ("the peers no longer read the output region")
+ * may be skipped (sync_before = 0) by a caller that alternates between TWO output regions and consumes
+ * each result before its next collective call: a peer can then be at most one call ahead, i.e. writing
+ * the other region.  reduce_scatter always opens with one; its closing one ("the peers have finished
+ * reading my input") may be skipped (sync_after = 0) under the same two-region discipline for inputs. */
+#define DGMC_SYM_MAX_BLOCKS 128
+#define DGMC_SYM_MAX_WORLD 8
+size_t dgmc_sym_pad_bytes(void);
+int dgmc_sym_all_reduce(const void* const* peer_bases, const void* multicast_base, int rank, int world,
+                        int64_t in_off, int64_t out_off, int64_t pad_off, int64_t n, dgmc_stream_t stream);
+int dgmc_sym_all_gather(const void* const* peer_bases, int rank, int world, const float* in, int64_t out_off,
+                        int64_t pad_off, int64_t block, int sync_before, dgmc_stream_t stream);
+int dgmc_sym_reduce_scatter(const void* const* peer_bases, int rank, int world, int64_t in_off, float* out,
+                            int64_t pad_off, int64_t block, int sync_after, dgmc_stream_t stream);
+/* number of handshakes that gave up so far on this device (synchronises the device); 0 in a healthy run */
+int dgmc_sym_timeouts(void);
+
 #ifdef __cplusplus
 }
 #endif
