@@ -35,25 +35,56 @@ def row_block(n_rows, rank, world):
     return lo, lo + base + (1 if rank < extra else 0)
 
 
+# messages up to this size go through the library's own peer-memory kernels (dgmc.symm / csrc/symm.cu:
+# latency-optimised), larger ones through NCCL's bandwidth-optimised ring
+PEER_MAX_BYTES = 64 << 20
+
+
+def _peer(group, device, nbytes, numel):
+    """PeerCollectives of the group for a message of nbytes, or None (CPU / gloo, no peer access,
+    message too large or not a multiple of 4 floats)."""
+    if device.type != 'cuda' or nbytes > PEER_MAX_BYTES or numel % 4 != 0 or numel == 0:
+        return None
+    from ..symm import PeerCollectives
+    return PeerCollectives.of(group, device, nbytes)
+
+
+def _sum_over_ranks(x, group):
+    """-> a fresh tensor holding the sum of x over the ranks (x itself may be the peer scratch)."""
+    pc = _peer(group, x.device, x.numel() * 4, x.numel()) if x.dtype == torch.float32 else None
+    if pc is None:
+        y = x.contiguous().clone()
+        dist.all_reduce(y, op=dist.ReduceOp.SUM, group=group)
+        return y
+    n = x.numel()
+    src = pc.scratch_in(1, n)
+    if x.data_ptr() != src.data_ptr():       # the producer may already have written into the scratch
+        src.copy_(x.reshape(1, n))
+    return pc.all_reduce(1, n).clone().view(x.shape)
+
+
 class _AllReduceSum(torch.autograd.Function):
     """y = sum over ranks of x; the adjoint of a sum whose result every rank consumes in a
     replicated computation is again the sum of the ranks' gradients."""
     @staticmethod
     def forward(ctx, x, group):
         ctx.group = group
-        y = x.contiguous().clone()
-        dist.all_reduce(y, op=dist.ReduceOp.SUM, group=group)
-        return y
+        return _sum_over_ranks(x, group)
 
     @staticmethod
     def backward(ctx, g):
-        g = g.contiguous().clone()
-        dist.all_reduce(g, op=dist.ReduceOp.SUM, group=ctx.group)
-        return g, None
+        return _sum_over_ranks(g, ctx.group), None
 
 
 def all_reduce_sum(x, group=None):
     return _AllReduceSum.apply(x, group)
+
+
+def transport_partial_buffer(n_t, r, device, group):
+    """Where ops.transport should write this rank's partial r_t so that the all-reduce needs no copy:
+    the peer scratch when peer-memory collectives are in use, else None (a fresh tensor)."""
+    pc = _peer(group, device, n_t * r * 4, n_t * r)
+    return None if pc is None else pc.scratch_in(1, n_t * r).view(n_t, r)
 
 
 class _AllGatherRows(torch.autograd.Function):
@@ -62,15 +93,24 @@ class _AllGatherRows(torch.autograd.Function):
     def forward(ctx, x, group):
         ctx.group = group
         x = x.contiguous()
-        out = x.new_empty(dist.get_world_size(group) * x.size(0), x.size(1))
+        world = dist.get_world_size(group)
+        pc = _peer(group, x.device, world * x.numel() * 4, x.numel()) if x.dtype == torch.float32 else None
+        if pc is not None:
+            return pc.all_gather(x).clone()
+        out = x.new_empty(world * x.size(0), x.size(1))
         dist.all_gather_into_tensor(out, x, group=group)
         return out
 
     @staticmethod
     def backward(ctx, g):
         world = dist.get_world_size(ctx.group)
+        rows, cols = g.size(0) // world, g.size(1)
+        pc = _peer(ctx.group, g.device, g.numel() * 4, rows * cols) if g.dtype == torch.float32 else None
+        if pc is not None:
+            pc.scratch_in(g.size(0), cols).copy_(g)
+            return pc.reduce_scatter(rows, cols), None
         g = g.contiguous()
-        out = g.new_empty(g.size(0) // world, g.size(1))
+        out = g.new_empty(rows, cols)
         dist.reduce_scatter_tensor(out, g, op=dist.ReduceOp.SUM, group=ctx.group)
         return out, None
 
@@ -146,9 +186,10 @@ def _pad_rows(x, n):
     return x if x.size(0) == n else torch.cat([x, x.new_zeros(n - x.size(0), x.size(1))], dim=0)
 
 
-def sharded_relcnn(psi, x_gathered, sp, group):
+def sharded_relcnn(psi, x_gathered, sp, group, masks=None):
     """RelCNN.forward (rel.py:80-92) for this rank's nodes only.  x_gathered: the layer-0 features of
-    ALL nodes in the gathered layout [world * n_max, C]; returns [n_loc, out_channels]."""
+    ALL nodes in the gathered layout [world * n_max, C]; masks: per layer the dropout factors of this
+    rank's nodes (see reference_dropout_masks) or None; returns [n_loc, out_channels]."""
     own = torch.arange(sp.n_loc, device=x_gathered.device) + dist.get_rank(group) * sp.n_max
     feats = [x_gathered[own]]
     full = x_gathered
@@ -161,11 +202,29 @@ def sharded_relcnn(psi, x_gathered, sp, group):
             # only reached in eval mode (MergedPair.mergeable): the running-statistics affine map
             # is per node, so the node shard applies it without communication (rel.py:86-87)
             h = psi.batch_norms[i](h)
+        if masks is not None:
+            h = h * masks[i]
         feats.append(h)
         if i + 1 < len(psi.convs):
             full = all_gather_rows(_pad_rows(h, sp.n_max), group)
     out = torch.cat(feats, dim=-1) if psi.cat else feats[-1]
     return ops.node_linear(out, psi.final.weight, psi.final.bias, key=('final', id(psi))) if psi.lin else out
+
+
+def reference_dropout_masks(psi, n_s, n_t, rows, device):
+    """The dropout factors (0 or 1 / (1 - p)) the single-process forward would draw for psi on the two
+    graphs, for the merged-pair rows `rows`, per layer.  The reference runs psi_1 on the source graph
+    (one F.dropout per layer, rel.py:88) and then on the target graph (dgmc.py:149-150); F.dropout's
+    mask depends only on the generator state and the tensor's shape, so drawing on tensors of ones in
+    that order consumes the stream exactly as the reference does — every rank draws the full masks
+    from the shared seed and keeps its rows."""
+    import torch.nn.functional as F
+    if not (psi.training and psi.dropout > 0):
+        return None
+    width = psi.convs[0].out_channels
+    per_graph = [[F.dropout(torch.ones(n, width, device=device), p=psi.dropout, training=True)
+                  for _ in psi.convs] for n in (n_s, n_t)]
+    return [torch.cat([per_graph[0][i], per_graph[1][i]], dim=0)[rows] for i in range(len(psi.convs))]
 
 
 class RowShardedDGMC(DGMC):
@@ -178,12 +237,16 @@ class RowShardedDGMC(DGMC):
     # (source + target) they cost more than the replicated psi_2 they save
     SHARD_PSI_MIN_NODES = 150000
 
-    def __init__(self, psi_1, psi_2, num_steps, k, detach=False, group=None, shard_psi='auto'):
+    def __init__(self, psi_1, psi_2, num_steps, k, detach=False, group=None, shard_psi='auto',
+                 shard_psi_1='auto'):
         super().__init__(psi_1, psi_2, num_steps, k=k, detach=detach)
         assert k >= 1, 'row sharding applies to the sparse variant (k >= 1)'
         self.group = group
         # node-shard psi_2 (RelCNN) instead of running it replicated: True / False / 'auto' (by size)
         self.shard_psi = shard_psi
+        # node-shard psi_1 (RelCNN without batch-norm statistics): each rank embeds its own source rows
+        # and a block of target nodes, layer outputs are all-gathered, h_t is all-gathered once
+        self.shard_psi_1 = shard_psi_1
 
     def _world(self):
         return dist.get_rank(self.group), dist.get_world_size(self.group)
@@ -192,25 +255,40 @@ class RowShardedDGMC(DGMC):
                  batch_t, y=None):
         assert batch_s is None and batch_t is None, 'row sharding handles one graph pair'
         rank, world = self._world()
-        h_s = self.psi_1(x_s, edge_index_s, edge_attr_s)
-        h_t = self.psi_1(x_t, edge_index_t, edge_attr_t)
-        if self.detach:
-            h_s, h_t = h_s.detach(), h_t.detach()
-        N_s, N_t, C = h_s.size(0), h_t.size(0), h_s.size(1)
+        from .rel import RelCNN
+        N_s, N_t = x_s.size(0), x_t.size(0)
         lo, hi = row_block(N_s, rank, world)
         n_loc = hi - lo
+        psi_1 = self.psi_1
+        shard_1 = world > 1 and isinstance(psi_1, RelCNN) and psi_1.lin and edge_attr_s is None and \
+            not (psi_1.batch_norm and psi_1.training) and self.shard_psi_1 in (True, 'auto')
+        if shard_1:
+            # psi_1 on this rank's nodes only (its rows of S + a block of target nodes); the neighbours'
+            # features of every layer come from an all-gather, h_t from one more
+            sp1 = ShardedPair.of(edge_index_s, edge_index_t, N_s, N_t, rank, world)
+            masks = reference_dropout_masks(psi_1, N_s, N_t, sp1.local, x_s.device)
+            h_own = sharded_relcnn(psi_1, torch.cat([x_s, x_t], dim=0)[sp1.src_of], sp1, self.group, masks)
+            if self.detach:
+                h_own = h_own.detach()
+            h_loc = h_own[:sp1.ns_loc]
+            h_t = all_gather_rows(_pad_rows(h_own[sp1.ns_loc:], sp1.nt_max), self.group)[sp1.pos_t]
+        else:
+            h_s = psi_1(x_s, edge_index_s, edge_attr_s)
+            h_t = psi_1(x_t, edge_index_t, edge_attr_t)
+            if self.detach:
+                h_s, h_t = h_s.detach(), h_t.detach()
+            h_loc = h_s[lo:hi]
+        C = h_t.size(1)
         R_in = self.psi_2.in_channels
         w1, b1, w2, b2 = self._hoisted_mlp()
         num_steps = self.num_steps or 0
         merged = ops.MergedPair.of(self.psi_2, self.training, edge_index_s, edge_index_t,
                                    edge_attr_s, edge_attr_t, N_s, N_t)
-        from .rel import RelCNN
         sp = None
         shard_psi = (N_s + N_t >= self.SHARD_PSI_MIN_NODES) if self.shard_psi == 'auto' else self.shard_psi
         if shard_psi and world > 1 and merged is not None and isinstance(self.psi_2, RelCNN):
             sp = ShardedPair.of(edge_index_s, edge_index_t, N_s, N_t, rank, world)
 
-        h_loc = h_s[lo:hi]
         S_idx = self.__top_k__(h_loc.unsqueeze(0), h_t.unsqueeze(0))  # [1, n_loc, k]
         if self.training and y is not None:
             # draw at the reference's full shape so every rank sees the same stream, keep own rows
@@ -233,8 +311,10 @@ class RowShardedDGMC(DGMC):
         S_0 = ops.softmax_k(S_hat)
         for _ in range(num_steps):
             S = ops.softmax_k(S_hat)
-            r_s = torch.randn((1, N_s, R_in), dtype=h_s.dtype, device=h_s.device).view(N_s, R_in)
-            r_t = all_reduce_sum(ops.transport(S, r_s[lo:hi], cand), self.group)
+            r_s = torch.randn((1, N_s, R_in), dtype=h_t.dtype, device=h_t.device).view(N_s, R_in)
+            # the partial transport goes straight into the buffer the peers' all-reduce kernels read
+            part = transport_partial_buffer(N_t, R_in, h_t.device, self.group)
+            r_t = all_reduce_sum(ops.transport(S, r_s[lo:hi], cand, out=part), self.group)
             if sp is not None:
                 # node-sharded psi_2: layer-0 features of every node in the gathered layout (local
                 # index_select: every rank holds r_s and the all-reduced r_t), then this rank's nodes
@@ -316,7 +396,10 @@ class RowShardedDGMC(DGMC):
         if not grads:
             return
         flat = torch.cat([g.reshape(-1) for g in grads])
-        dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group)
+        pad = (-flat.numel()) % 4
+        if pad:
+            flat = torch.cat([flat, flat.new_zeros(pad)])
+        flat = _sum_over_ranks(flat, self.group)
         off = 0
         for g in grads:
             g.copy_(flat[off:off + g.numel()].view_as(g))

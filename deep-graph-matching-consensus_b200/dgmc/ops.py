@@ -369,13 +369,13 @@ def gather_dot(a, b, cand):
 # --------------------------------------------------------------------------------------------
 class _Transport(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, S, r_s, cand):
+    def forward(ctx, S, r_s, cand, out):
         S, r_s = _f32(S), _f32(r_s)
         tptr, perm, seg_of = cand.csr
         ctx.cand = cand
         ctx.save_for_backward(S, r_s)
         return segment_gather(r_s, cand.targets, perm, ptr=tptr, src_div=cand.k, w_index=perm,
-                              w=S.view(-1), seg_of=seg_of)
+                              w=S.view(-1), seg_of=seg_of, out=out)
 
     @staticmethod
     def backward(ctx, g):
@@ -386,13 +386,14 @@ class _Transport(torch.autograd.Function):
             dS = _gather_dot_raw(r_s, g, cand.idx)
         if ctx.needs_input_grad[1]:  # dr_s[m] = sum_j S[m, j] g[idx[m, j]]
             dr = segment_gather(g, cand.m, cand.idx.view(-1), fixed_len=cand.k, w=S.view(-1))
-        return dS, dr, None
+        return dS, dr, None, None
 
 
-def transport(S, r_s, cand):
+def transport(S, r_s, cand, out=None):
     """r_t[t] = sum_{(m,j): idx[m,j] = t} S[m,j] r_s[m]  (scatter_add at dgmc.py:209-212),
-    computed as a deterministic by-target segmented gather.  -> [B*N_t, R]."""
-    return _Transport.apply(S, r_s, cand)
+    computed as a deterministic by-target segmented gather.  -> [B*N_t, R].  `out`: write the result
+    there (the row-sharded path hands in the peer-memory buffer its all-reduce reads)."""
+    return _Transport.apply(S, r_s, cand, out)
 
 
 # --------------------------------------------------------------------------------------------

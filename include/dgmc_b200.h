@@ -278,7 +278,7 @@ int dgmc_dense_consensus_bwd(const float* g, const float* ps, const float* pt, c
 /* ---- multi-GPU: collectives of the row-sharded path over NVLink peer memory ---------------------
  * No counterpart in the reference (single process).  One process per GPU; the ranks share ONE symmetric
  * allocation (same size and layout on every rank, every rank's copy mapped into every process, e.g.
- * torch.distributed._symmetric_memory).  peer_bases: HOST array of `world` device pointers, entry q =
+ * a CUDA VMM allocation whose handles the processes exchanged).  peer_bases: HOST array of `world` device pointers, entry q =
  * base of rank q's copy as mapped in THIS process; *_off: byte offsets inside the allocation, equal on
  * all ranks.  pad_off: dgmc_sym_pad_bytes() bytes of flag words, zeroed once before the first call.
  * Every rank must issue the same calls in the same order (they handshake block by block; a rank that

@@ -35,7 +35,8 @@ def _worker(rank, world, port, out):
 
         def build(cls):
             torch.manual_seed(0)
-            m = cls(RelCNN(32, 48, 2, dropout=0.0), RelCNN(16, 16, 2), num_steps=3, k=6).cuda().train()
+            # psi_1 with dropout: the sharded path must reproduce the single-process mask stream
+            m = cls(RelCNN(32, 48, 2, dropout=0.5), RelCNN(16, 16, 2), num_steps=3, k=6).cuda().train()
             return m
 
         single = build(DGMC)
@@ -44,9 +45,10 @@ def _worker(rank, world, port, out):
         l1 = single.loss(S1, y)
         l1.backward()
         floor = 1e-5 * max(p.grad.abs().max().item() for p in single.parameters() if p.grad is not None)
-        for shard_psi in (False, True):   # psi_2 replicated / node-sharded with all-gathers
+        # psi_2 replicated / node-sharded with all-gathers; psi_1 replicated / node-sharded
+        for shard_psi, shard_psi_1 in ((False, False), (True, False), (False, True), (True, True)):
             sharded = build(RowShardedDGMC)
-            sharded.shard_psi = shard_psi
+            sharded.shard_psi, sharded.shard_psi_1 = shard_psi, shard_psi_1
             torch.manual_seed(123)
             _, S2 = sharded(x_s, e_s, None, None, x_t, e_t, None, None, y)
             share = sharded.loss(S2, y)
@@ -66,7 +68,11 @@ def _worker(rank, world, port, out):
                     assert q.grad is None
                     continue
                 scale = p.grad.abs().max().item()
-                assert (p.grad - q.grad).abs().max().item() <= 5e-4 * scale + floor, (shard_psi, n)
+                assert (p.grad - q.grad).abs().max().item() <= 5e-4 * scale + floor, (shard_psi, shard_psi_1, n)
+        from dgmc.symm import PeerCollectives
+        pc = PeerCollectives._by_group.get(id(None))
+        assert pc, 'peer-memory collectives were not used'
+        assert pc.timeouts() == 0
         out.put((rank, 'ok'))
     except Exception:  # pragma: no cover
         import traceback
