@@ -133,32 +133,44 @@ __global__ void __launch_bounds__(SYM_THREADS) sym_all_reduce_kernel(const SymPe
     sym_block_barrier(p, pad_off, 1, rank, world);       // every rank's slice has landed everywhere
 }
 
-// out_r[rank * block4 + i] = in[i] on every rank r
+// A rank's part of a gathered tensor: up to two runs (float4 units, relative to the tensor's start);
+// the rank's local buffer holds run 0 then run 1, contiguously.  Equal blocks in rank order are the
+// special case {rank * block, block, 0, 0}; the node-sharded psi networks use two runs — the rank's
+// source nodes and its target nodes in the natural [source ; target] node order.
+struct SymRuns {
+    long long at0, len0, at1, len1;
+    __device__ __forceinline__ long long where(long long i) const { return i < len0 ? at0 + i : at1 + (i - len0); }
+};
+
+// out_r[runs(i)] = in[i] on every rank r
 __global__ void __launch_bounds__(SYM_THREADS) sym_all_gather_kernel(const SymPeers p, int rank, int world,
                                                                      const float4* __restrict__ in,
                                                                      long long out_off, long long pad_off,
-                                                                     long long block4, int sync_before) {
+                                                                     const SymRuns runs, int sync_before) {
     // the opening handshake (peers have let go of the output region) is not needed when the caller
     // alternates between two output regions: see dgmc_b200.h
     if (sync_before) sym_block_barrier(p, pad_off, 0, rank, world);
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < block4;
+    const long long total = runs.len0 + runs.len1;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
          i += (long long)gridDim.x * blockDim.x) {
         const float4 v = in[i];
+        const long long j = runs.where(i);
         for (int q = 0; q < world; ++q)
-            __stcg(reinterpret_cast<float4*>(p.base[q] + out_off) + (long long)rank * block4 + i, v);
+            __stcg(reinterpret_cast<float4*>(p.base[q] + out_off) + j, v);
     }
     sym_block_barrier(p, pad_off, 1, rank, world);
 }
 
-// out[i] = sum_p in_p[rank * block4 + i]
+// out[i] = sum_p in_p[runs(i)]
 __global__ void __launch_bounds__(SYM_THREADS) sym_reduce_scatter_kernel(const SymPeers p, int rank, int world,
                                                                          long long in_off, float4* __restrict__ out,
-                                                                         long long pad_off, long long block4,
+                                                                         long long pad_off, const SymRuns runs,
                                                                          int sync_after) {
     sym_block_barrier(p, pad_off, 0, rank, world);       // every rank's input is complete
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < block4;
+    const long long total = runs.len0 + runs.len1;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
          i += (long long)gridDim.x * blockDim.x) {
-        const long long j = (long long)rank * block4 + i;
+        const long long j = runs.where(i);
         float4 acc = __ldcg(reinterpret_cast<const float4*>(p.base[0] + in_off) + j);
         for (int q = 1; q < world; ++q)
             acc = add4(acc, __ldcg(reinterpret_cast<const float4*>(p.base[q] + in_off) + j));
@@ -210,29 +222,42 @@ extern "C" int dgmc_sym_all_reduce(const void* const* peer_bases, const void* mu
     return check_launch("sym_all_reduce");
 }
 
+static int sym_runs(SymRuns* r, int64_t at0, int64_t len0, int64_t at1, int64_t len1, int64_t max_len,
+                    const char* what) {
+    if (at0 < 0 || len0 < 0 || at1 < 0 || len1 < 0 || (at0 | len0 | at1 | len1 | max_len) % 4 != 0 ||
+        max_len < len0 + len1) {
+        set_error("%s: runs must be non-negative multiples of 4 floats, max_len >= len0 + len1", what);
+        return DGMC_ERR_INVALID;
+    }
+    r->at0 = at0 / 4; r->len0 = len0 / 4; r->at1 = at1 / 4; r->len1 = len1 / 4;
+    return DGMC_OK;
+}
+
 extern "C" int dgmc_sym_all_gather(const void* const* peer_bases, int rank, int world, const float* in,
-                                   int64_t out_off, int64_t pad_off, int64_t block, int sync_before,
-                                   dgmc_stream_t stream) {
+                                   int64_t out_off, int64_t pad_off, int64_t at0, int64_t len0, int64_t at1,
+                                   int64_t len1, int64_t max_len, int sync_before, dgmc_stream_t stream) {
     SymPeers p;
+    SymRuns r;
     if (int e = sym_peers(&p, peer_bases, rank, world, "sym_all_gather")) return e;
-    DGMC_REQUIRE(in && block >= 0 && block % 4 == 0 && out_off % 16 == 0 && pad_off % 4 == 0 &&
-                     (reinterpret_cast<uintptr_t>(in) & 15) == 0,
-                 "sym_all_gather: block must be a multiple of 4 floats, pointers / offsets 16-byte aligned");
-    sym_all_gather_kernel<<<sym_grid(block / 4), SYM_THREADS, 0, stream>>>(
-        p, rank, world, reinterpret_cast<const float4*>(in), out_off, pad_off, block / 4, sync_before);
+    if (int e = sym_runs(&r, at0, len0, at1, len1, max_len, "sym_all_gather")) return e;
+    DGMC_REQUIRE(in && out_off % 16 == 0 && pad_off % 4 == 0 && (reinterpret_cast<uintptr_t>(in) & 15) == 0,
+                 "sym_all_gather: pointers / offsets must be 16-byte aligned");
+    sym_all_gather_kernel<<<sym_grid(max_len / 4), SYM_THREADS, 0, stream>>>(
+        p, rank, world, reinterpret_cast<const float4*>(in), out_off, pad_off, r, sync_before);
     return check_launch("sym_all_gather");
 }
 
 extern "C" int dgmc_sym_reduce_scatter(const void* const* peer_bases, int rank, int world, int64_t in_off,
-                                       float* out, int64_t pad_off, int64_t block, int sync_after,
-                                       dgmc_stream_t stream) {
+                                       float* out, int64_t pad_off, int64_t at0, int64_t len0, int64_t at1,
+                                       int64_t len1, int64_t max_len, int sync_after, dgmc_stream_t stream) {
     SymPeers p;
+    SymRuns r;
     if (int e = sym_peers(&p, peer_bases, rank, world, "sym_reduce_scatter")) return e;
-    DGMC_REQUIRE(out && block >= 0 && block % 4 == 0 && in_off % 16 == 0 && pad_off % 4 == 0 &&
-                     (reinterpret_cast<uintptr_t>(out) & 15) == 0,
-                 "sym_reduce_scatter: block must be a multiple of 4 floats, pointers / offsets 16-byte aligned");
-    sym_reduce_scatter_kernel<<<sym_grid(block / 4), SYM_THREADS, 0, stream>>>(
-        p, rank, world, in_off, reinterpret_cast<float4*>(out), pad_off, block / 4, sync_after);
+    if (int e = sym_runs(&r, at0, len0, at1, len1, max_len, "sym_reduce_scatter")) return e;
+    DGMC_REQUIRE(out && in_off % 16 == 0 && pad_off % 4 == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0,
+                 "sym_reduce_scatter: pointers / offsets must be 16-byte aligned");
+    sym_reduce_scatter_kernel<<<sym_grid(max_len / 4), SYM_THREADS, 0, stream>>>(
+        p, rank, world, in_off, reinterpret_cast<float4*>(out), pad_off, r, sync_after);
     return check_launch("sym_reduce_scatter");
 }
 

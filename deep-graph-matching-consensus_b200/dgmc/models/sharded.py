@@ -35,9 +35,9 @@ def row_block(n_rows, rank, world):
     return lo, lo + base + (1 if rank < extra else 0)
 
 
-# messages up to this size go through the library's own peer-memory kernels (dgmc.symm / csrc/symm.cu:
+# messages up to this size go through the library's own peer-memory kernels (dgmc.symm / csrc/symm.cu;
 # latency-optimised), larger ones through NCCL's bandwidth-optimised ring
-PEER_MAX_BYTES = 64 << 20
+PEER_MAX_BYTES = 2304 << 20
 
 
 def _peer(group, device, nbytes, numel):
@@ -87,68 +87,33 @@ def transport_partial_buffer(n_t, r, device, group):
     return None if pc is None else pc.scratch_in(1, n_t * r).view(n_t, r)
 
 
-class _AllGatherRows(torch.autograd.Function):
-    """[n, c] on every rank -> [world * n, c]; adjoint: reduce-scatter of the gradient."""
-    @staticmethod
-    def forward(ctx, x, group):
-        ctx.group = group
-        x = x.contiguous()
-        world = dist.get_world_size(group)
-        pc = _peer(group, x.device, world * x.numel() * 4, x.numel()) if x.dtype == torch.float32 else None
-        if pc is not None:
-            return pc.all_gather(x).clone()
-        out = x.new_empty(world * x.size(0), x.size(1))
-        dist.all_gather_into_tensor(out, x, group=group)
-        return out
-
-    @staticmethod
-    def backward(ctx, g):
-        world = dist.get_world_size(ctx.group)
-        rows, cols = g.size(0) // world, g.size(1)
-        pc = _peer(ctx.group, g.device, g.numel() * 4, rows * cols) if g.dtype == torch.float32 else None
-        if pc is not None:
-            pc.scratch_in(g.size(0), cols).copy_(g)
-            return pc.reduce_scatter(rows, cols), None
-        g = g.contiguous()
-        out = g.new_empty(rows, cols)
-        dist.reduce_scatter_tensor(out, g, op=dist.ReduceOp.SUM, group=ctx.group)
-        return out, None
-
-
-def all_gather_rows(x, group=None):
-    return _AllGatherRows.apply(x, group)
-
-
 class ShardedPair(object):
     """Node partition of the merged (source + target) graph over the ranks, and this rank's slice
     of the RelConv aggregation operator.
 
-    Gathered layout: rank q contributes a block of `n_max` rows = [its source nodes | its target
-    nodes | padding]; `pos[v]` is the row of merged node v in that layout.  `rel` is the
-    [3 n_loc, world * n_max] operator (see ops._RelAggregate) restricted to this rank's nodes with
-    columns in the gathered layout.  Built once per (edge_index_s, edge_index_t) and cached."""
+    Rank q owns the source nodes row_block(N_s, q) — the same rows of S it owns — and the target nodes
+    row_block(N_t, q).  Node features keep the NATURAL merged order [source nodes ; target nodes]
+    everywhere: a rank's part of a gathered [N_s + N_t, C] tensor is two runs of rows (`runs`), which
+    the peer-memory all-gather / reduce-scatter kernels address directly, so there is no permutation on
+    either side.  `rel` is the [3 n_loc, N_s + N_t] operator (see ops._RelAggregate) restricted to this
+    rank's nodes.  Built once per (edge_index_s, edge_index_t) with data-dependent shapes (boolean
+    masks), hence cached and not capturable: see RowShardedDGMC._node_shard."""
     _cache = {}
 
     def __init__(self, e_s, e_t, n_s, n_t, rank, world):
         dev = e_s.device
-        blocks_s = [row_block(n_s, q, world) for q in range(world)]
-        blocks_t = [row_block(n_t, q, world) for q in range(world)]
-        self.n_max = max((b[1] - b[0]) + (c[1] - c[0]) for b, c in zip(blocks_s, blocks_t))
-        self.nt_max = max(c[1] - c[0] for c in blocks_t)
-        n = n_s + n_t
-        pos = torch.empty(n, dtype=torch.long, device=dev)
-        pos_t = torch.empty(n_t, dtype=torch.long, device=dev)   # target -> row of the gathered P_t
-        for q, (b, c) in enumerate(zip(blocks_s, blocks_t)):
-            pos[b[0]:b[1]] = q * self.n_max + torch.arange(b[1] - b[0], device=dev)
-            pos[n_s + c[0]:n_s + c[1]] = q * self.n_max + (b[1] - b[0]) + torch.arange(c[1] - c[0], device=dev)
-            pos_t[c[0]:c[1]] = q * self.nt_max + torch.arange(c[1] - c[0], device=dev)
-        self.pos_t = pos_t
-        src_of = torch.zeros(world * self.n_max, dtype=torch.long, device=dev)  # gathered row -> merged node
-        src_of[pos] = torch.arange(n, device=dev)
-        self.src_of = src_of
-        (lo_s, hi_s), (lo_t, hi_t) = blocks_s[rank], blocks_t[rank]
+        self.world, self.rank, self.n_s, self.n_t, self.n = world, rank, n_s, n_t, n_s + n_t
+        self.blocks_s = [row_block(n_s, q, world) for q in range(world)]
+        self.blocks_t = [row_block(n_t, q, world) for q in range(world)]
+        self.ns_max = max(b[1] - b[0] for b in self.blocks_s)
+        self.nt_max = max(c[1] - c[0] for c in self.blocks_t)
+        (lo_s, hi_s), (lo_t, hi_t) = self.blocks_s[rank], self.blocks_t[rank]
         self.ns_loc, self.nt_loc = hi_s - lo_s, hi_t - lo_t
         self.n_loc = self.ns_loc + self.nt_loc
+        self.runs = ((lo_s, self.ns_loc), (n_s + lo_t, self.nt_loc))      # in a [n_s + n_t, C] tensor
+        self.runs_t = ((lo_t, self.nt_loc), (0, 0))                       # in a [n_t, C] tensor
+        self.max_rows = max((b[1] - b[0]) + (c[1] - c[0]) for b, c in zip(self.blocks_s, self.blocks_t))
+        n = self.n
         local = torch.cat([torch.arange(lo_s, hi_s, device=dev), n_s + torch.arange(lo_t, hi_t, device=dev)])
         self.local = local
         loc_of = torch.full((n, ), -1, dtype=torch.long, device=dev)
@@ -160,10 +125,10 @@ class ShardedPair(object):
         m_in, m_out = loc_of[dst] >= 0, loc_of[src] >= 0
         rows = torch.cat([3 * torch.arange(self.n_loc, device=dev), 3 * loc_of[dst[m_in]] + 1,
                           3 * loc_of[src[m_out]] + 2]).to(torch.int32)
-        cols = torch.cat([pos[local], pos[src[m_in]], pos[dst[m_out]]]).to(torch.int32)
+        cols = torch.cat([local, src[m_in], dst[m_out]]).to(torch.int32)
         w = torch.cat([torch.ones(self.n_loc, device=dev), inv_in[dst[m_in]], inv_out[src[m_out]]])
         rel = type('RelSlice', (), {})()
-        rel.n_out, rel.n_in = self.n_loc, world * self.n_max
+        rel.n_out, rel.n_in = self.n_loc, n
         rel.f_ptr, perm, rel.f_seg = ops.csr_build(rows, 3 * rel.n_out, True)
         rel.f_src, rel.f_w = cols[perm.long()].contiguous(), w[perm.long()].contiguous()
         rel.b_ptr, perm, rel.b_seg = ops.csr_build(cols, rel.n_in, True)
@@ -174,7 +139,11 @@ class ShardedPair(object):
     def of(cls, e_s, e_t, n_s, n_t, rank, world):
         key = (e_s.data_ptr(), e_t.data_ptr(), e_s._version, e_t._version, n_s, n_t, rank, world)
         hit = cls._cache.get(key)
+        if ops.DYNAMIC_STRUCTURE[0]:
+            return None          # the step must follow its inputs' edge lists: no cached structures
         if hit is None or hit[0] is not e_s or hit[1] is not e_t:
+            if torch.cuda.is_current_stream_capturing():
+                return None      # data-dependent shapes: cannot be built inside a CUDA-graph capture
             if len(cls._cache) > 16:
                 cls._cache.clear()
             hit = (e_s, e_t, cls(e_s, e_t, n_s, n_t, rank, world))
@@ -182,17 +151,85 @@ class ShardedPair(object):
         return hit[2]
 
 
+ops._EXTRA_CACHES.append(ShardedPair._cache)
+
+
 def _pad_rows(x, n):
     return x if x.size(0) == n else torch.cat([x, x.new_zeros(n - x.size(0), x.size(1))], dim=0)
 
 
-def sharded_relcnn(psi, x_gathered, sp, group, masks=None):
-    """RelCNN.forward (rel.py:80-92) for this rank's nodes only.  x_gathered: the layer-0 features of
-    ALL nodes in the gathered layout [world * n_max, C]; masks: per layer the dropout factors of this
-    rank's nodes (see reference_dropout_masks) or None; returns [n_loc, out_channels]."""
-    own = torch.arange(sp.n_loc, device=x_gathered.device) + dist.get_rank(group) * sp.n_max
-    feats = [x_gathered[own]]
-    full = x_gathered
+class _AllGatherNodes(torch.autograd.Function):
+    """This rank's rows of a node-feature tensor -> the whole tensor in natural node order on every
+    rank; adjoint: every rank keeps the sum over ranks of its own rows of the gradient (reduce-scatter).
+    part = 'all': x [n_loc, C] -> [N_s + N_t, C]; part = 't': x [nt_loc, C] -> [N_t, C].
+    keep: the result outlives the next collective (it is copied out of the peer scratch)."""
+    @staticmethod
+    def forward(ctx, x, sp, group, part, keep):
+        ctx.sp, ctx.group, ctx.part = sp, group, part
+        x = x.contiguous()
+        c = x.size(1)
+        runs, total, max_rows = (sp.runs, sp.n, sp.max_rows) if part == 'all' else (sp.runs_t, sp.n_t, sp.nt_max)
+        pc = _peer(group, x.device, total * c * 4, 4 * c) if x.dtype == torch.float32 else None
+        if pc is not None:
+            full = pc.all_gather(x, runs, total, max_rows)
+            return full.clone() if keep else full
+        # torch.distributed: equal padded blocks, then the natural order by static slices
+        if part == 'all':
+            blk = torch.cat([_pad_rows(x[:sp.ns_loc], sp.ns_max), _pad_rows(x[sp.ns_loc:], sp.nt_max)], dim=0)
+        else:
+            blk = _pad_rows(x, sp.nt_max)
+        m = blk.size(0)
+        g = x.new_empty(sp.world * m, c)
+        dist.all_gather_into_tensor(g, blk, group=group)
+        pieces = []
+        if part == 'all':
+            pieces += [g[q * m:q * m + (b[1] - b[0])] for q, b in enumerate(sp.blocks_s)]
+            pieces += [g[q * m + sp.ns_max:q * m + sp.ns_max + (t[1] - t[0])] for q, t in enumerate(sp.blocks_t)]
+        else:
+            pieces += [g[q * m:q * m + (t[1] - t[0])] for q, t in enumerate(sp.blocks_t)]
+        return torch.cat(pieces, dim=0)
+
+    @staticmethod
+    def backward(ctx, g):
+        sp, group, part = ctx.sp, ctx.group, ctx.part
+        c = g.size(1)
+        runs, max_rows = (sp.runs, sp.max_rows) if part == 'all' else (sp.runs_t, sp.nt_max)
+        rows = runs[0][1] + runs[1][1]
+        pc = _peer(group, g.device, g.numel() * 4, 4 * c) if g.dtype == torch.float32 else None
+        if pc is not None:
+            pc.scratch_in(g.size(0), c).copy_(g)
+            return pc.reduce_scatter(rows, c, runs, max_rows), None, None, None, None
+        zeros = g.new_zeros
+        blocks = []
+        for q in range(sp.world):
+            (a, b), (t0, t1) = sp.blocks_s[q], sp.blocks_t[q]
+            if part == 'all':
+                blocks += [g[a:b], zeros(sp.ns_max - (b - a), c), g[sp.n_s + t0:sp.n_s + t1],
+                           zeros(sp.nt_max - (t1 - t0), c)]
+            else:
+                blocks += [g[t0:t1], zeros(sp.nt_max - (t1 - t0), c)]
+        padded = torch.cat(blocks, dim=0)
+        m = padded.size(0) // sp.world
+        out = g.new_empty(m, c)
+        dist.reduce_scatter_tensor(out, padded, op=dist.ReduceOp.SUM, group=group)
+        if part == 'all':
+            out = torch.cat([out[:sp.ns_loc], out[sp.ns_max:sp.ns_max + sp.nt_loc]], dim=0)
+        else:
+            out = out[:sp.nt_loc]
+        return out, None, None, None, None
+
+
+def all_gather_nodes(x, sp, group=None, part='all', keep=True):
+    return _AllGatherNodes.apply(x, sp, group, part, keep)
+
+
+def sharded_relcnn(psi, x_full, sp, group, masks=None):
+    """RelCNN.forward (rel.py:80-92) for this rank's nodes only.  x_full: the layer-0 features of ALL
+    nodes, natural merged order [N_s + N_t, C]; masks: per layer the dropout factors of this rank's
+    nodes (see reference_dropout_masks) or None; returns [n_loc, out_channels]."""
+    feats = [torch.cat([x_full[sp.runs[0][0]:sp.runs[0][0] + sp.ns_loc],
+                        x_full[sp.runs[1][0]:sp.runs[1][0] + sp.nt_loc]], dim=0)]
+    full = x_full
     for i, conv in enumerate(psi.convs):
         stacked = ops.rel_aggregate_op(full, sp.rel)                      # [n_loc, 3 C]
         weight = ops.region_cached(('relconv', id(conv)), lambda c=conv: torch.cat(
@@ -206,7 +243,8 @@ def sharded_relcnn(psi, x_gathered, sp, group, masks=None):
             h = h * masks[i]
         feats.append(h)
         if i + 1 < len(psi.convs):
-            full = all_gather_rows(_pad_rows(h, sp.n_max), group)
+            # consumed by the next layer's aggregation right away (which keeps no reference to it)
+            full = all_gather_nodes(h, sp, group, 'all', keep=False)
     out = torch.cat(feats, dim=-1) if psi.cat else feats[-1]
     return ops.node_linear(out, psi.final.weight, psi.final.bias, key=('final', id(psi))) if psi.lin else out
 
@@ -262,16 +300,19 @@ class RowShardedDGMC(DGMC):
         psi_1 = self.psi_1
         shard_1 = world > 1 and isinstance(psi_1, RelCNN) and psi_1.lin and edge_attr_s is None and \
             not (psi_1.batch_norm and psi_1.training) and self.shard_psi_1 in (True, 'auto')
-        if shard_1:
+        # the node partition is built with data-dependent shapes: it is cached per edge list and cannot
+        # be (re)built inside a CUDA-graph capture — a step captured with structure_is_static=False
+        # therefore runs psi replicated (ShardedPair.of returns None there)
+        sp1 = ShardedPair.of(edge_index_s, edge_index_t, N_s, N_t, rank, world) if shard_1 else None
+        if sp1 is not None:
             # psi_1 on this rank's nodes only (its rows of S + a block of target nodes); the neighbours'
             # features of every layer come from an all-gather, h_t from one more
-            sp1 = ShardedPair.of(edge_index_s, edge_index_t, N_s, N_t, rank, world)
             masks = reference_dropout_masks(psi_1, N_s, N_t, sp1.local, x_s.device)
-            h_own = sharded_relcnn(psi_1, torch.cat([x_s, x_t], dim=0)[sp1.src_of], sp1, self.group, masks)
+            h_own = sharded_relcnn(psi_1, torch.cat([x_s, x_t], dim=0), sp1, self.group, masks)
             if self.detach:
                 h_own = h_own.detach()
             h_loc = h_own[:sp1.ns_loc]
-            h_t = all_gather_rows(_pad_rows(h_own[sp1.ns_loc:], sp1.nt_max), self.group)[sp1.pos_t]
+            h_t = all_gather_nodes(h_own[sp1.ns_loc:], sp1, self.group, 't')
         else:
             h_s = psi_1(x_s, edge_index_s, edge_attr_s)
             h_t = psi_1(x_t, edge_index_t, edge_attr_t)
@@ -316,13 +357,12 @@ class RowShardedDGMC(DGMC):
             part = transport_partial_buffer(N_t, R_in, h_t.device, self.group)
             r_t = all_reduce_sum(ops.transport(S, r_s[lo:hi], cand, out=part), self.group)
             if sp is not None:
-                # node-sharded psi_2: layer-0 features of every node in the gathered layout (local
-                # index_select: every rank holds r_s and the all-reduced r_t), then this rank's nodes
-                x0 = torch.cat([r_s, r_t], dim=0)[sp.src_of]
-                o_loc = sharded_relcnn(self.psi_2, x0, sp, self.group)             # [n_loc, R_out]
+                # node-sharded psi_2: every rank holds the layer-0 features of all nodes (r_s from the
+                # shared seed, the all-reduced r_t) and computes the layers for its own nodes
+                o_loc = sharded_relcnn(self.psi_2, torch.cat([r_s, r_t], dim=0), sp, self.group)   # [n_loc, R_out]
                 p_loc = ops.node_linear(o_loc, w1, key=('mlp0', id(self)))
                 p_s_loc = p_loc[:sp.ns_loc] + b1
-                p_t = all_gather_rows(_pad_rows(p_loc[sp.ns_loc:], sp.nt_max), self.group)[sp.pos_t]
+                p_t = all_gather_nodes(p_loc[sp.ns_loc:], sp, self.group, 't')
                 S_hat = ops.diff_mlp(S_hat, p_s_loc, p_t, w2, b2, cand)
                 continue
             # psi_2 replicated on the merged pair (this package's RelCNN / SplineCNN without batch-norm

@@ -248,11 +248,29 @@ class MergedPair(object):
         return hit[1]
 
 
+_EXTRA_CACHES = []   # structure caches of other modules (the node partition of the sharded path)
+
+# Set while a step is warmed up / captured that must rebuild every graph structure from its inputs on
+# each replay (GraphedTrainStep(structure_is_static=False)): structures whose construction has
+# data-dependent shapes (the node partition of the sharded path) are then not used at all.
+DYNAMIC_STRUCTURE = [False]
+
+
+class dynamic_structure(object):
+    def __enter__(self):
+        self.prev, DYNAMIC_STRUCTURE[0] = DYNAMIC_STRUCTURE[0], True
+
+    def __exit__(self, *exc):
+        DYNAMIC_STRUCTURE[0] = self.prev
+
+
 def clear_caches():
-    """Forget cached graph structures (CSR, spline bases, merged pairs)."""
+    """Forget cached graph structures (CSR, spline bases, merged pairs, node partitions)."""
     GraphCSR._cache.clear()
     SplineBasis._cache.clear()
     MergedPair._cache.clear()
+    for cache in _EXTRA_CACHES:
+        cache.clear()
 
 
 class Candidates(object):

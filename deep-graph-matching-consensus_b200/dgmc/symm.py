@@ -73,24 +73,36 @@ class PeerCollectives(object):
              self.out_off + self.flip_out * self.scratch_bytes, 0, n, stream_ptr())
         return self.scratch_out(rows, cols)
 
-    def all_gather(self, x):
-        """x [n, c] (same shape on every rank, any memory) -> scratch_out view [world * n, c]."""
+    def all_gather(self, x, runs=None, total_rows=None, max_rows=None):
+        """x [n, c] (any memory) -> scratch_out view of the gathered tensor.  Default: equal blocks in rank
+        order, [world * n, c].  runs = ((row0, n0), (row1, n1)): this rank's rows are rows row0.. and
+        row1.. of a [total_rows, c] tensor (x holds them in that order); max_rows: the largest n0 + n1
+        over the ranks."""
         x = x.contiguous()
-        n = x.numel()
-        assert n % 4 == 0 and x.dtype == torch.float32
+        c = x.size(1)
+        assert x.dtype == torch.float32 and c % 4 == 0
+        if runs is None:
+            runs, total_rows, max_rows = ((self.rank * x.size(0), x.size(0)), (0, 0)), self.world * x.size(0), x.size(0)
+        (r0, n0), (r1, n1) = runs
+        assert n0 + n1 == x.size(0) and total_rows * c * 4 <= self.scratch_bytes
         self.flip_out ^= 1     # the other region: peers may still be reading the previous result
         call('dgmc_sym_all_gather', self.bases, self.rank, self.world, x,
-             self.out_off + self.flip_out * self.scratch_bytes, 0, n, 0, stream_ptr())
-        return self.scratch_out(self.world * x.size(0), x.size(1))
+             self.out_off + self.flip_out * self.scratch_bytes, 0, r0 * c, n0 * c, r1 * c, n1 * c, max_rows * c,
+             0, stream_ptr())
+        return self.scratch_out(total_rows, c)
 
-    def reduce_scatter(self, rows, cols):
-        """Every rank has written [world * rows, cols] into scratch_in -> this rank's summed block, a
-        fresh tensor [rows, cols]."""
-        n = rows * cols
-        assert n % 4 == 0
+    def reduce_scatter(self, rows, cols, runs=None, max_rows=None):
+        """Every rank has written the whole tensor into scratch_in -> this rank's summed part, a fresh
+        tensor [rows, cols] (default: block `rank` of `world` equal blocks; else its `runs`)."""
+        assert cols % 4 == 0
+        if runs is None:
+            runs, max_rows = ((self.rank * rows, rows), (0, 0)), rows
+        (r0, n0), (r1, n1) = runs
+        assert n0 + n1 == rows
         out = torch.empty(rows, cols, dtype=torch.float32, device=self.buf.device)
         call('dgmc_sym_reduce_scatter', self.bases, self.rank, self.world,
-             self.in_off + self.flip_in * self.scratch_bytes, out, 0, n, 0, stream_ptr())
+             self.in_off + self.flip_in * self.scratch_bytes, out, 0, r0 * cols, n0 * cols, r1 * cols, n1 * cols,
+             max_rows * cols, 0, stream_ptr())
         self.flip_in ^= 1      # peers may still be reading this input: the next one goes to the other region
         return out
 

@@ -35,9 +35,11 @@ class GraphedTrainStep(object):
         self.structure_is_static = structure_is_static
         self.graph = torch.cuda.CUDAGraph()
 
+        import contextlib
+        dynamic = contextlib.nullcontext if structure_is_static else ops.dynamic_structure
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
-        with torch.cuda.stream(side):
+        with torch.cuda.stream(side), dynamic():
             for _ in range(warmup):
                 self._step()
         torch.cuda.current_stream().wait_stream(side)
@@ -48,7 +50,7 @@ class GraphedTrainStep(object):
         # CUDA events while this thread captures: only this thread's calls may be checked
         import torch.distributed as dist
         mode = 'thread_local' if dist.is_available() and dist.is_initialized() else 'global'
-        with torch.cuda.graph(self.graph, capture_error_mode=mode):
+        with torch.cuda.graph(self.graph, capture_error_mode=mode), dynamic():
             self.loss = self._step()
         if not structure_is_static:
             ops.clear_caches()  # entries made during capture point into the graph's private pool

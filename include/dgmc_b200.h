@@ -286,9 +286,14 @@ int dgmc_dense_consensus_bwd(const float* g, const float* ps, const float* pt, c
  * DGMC_SYM_MAX_WORLD ranks.  Sums are taken in rank order 0, 1, ... by exactly one rank per element, so
  * all ranks receive bit-identical results.
  *   all_reduce:      out_r[0:n] = sum_q in_q[0:n] on every rank r            (the r_t all-reduce)
- *   all_gather:      out_r[rank*block : (rank+1)*block] = in (local pointer)  (layer features of psi_2 / o_t)
- *   reduce_scatter:  out (local pointer) [0:block] = sum_q in_q[rank*block : (rank+1)*block]
- * n and block in floats, multiples of 4.  multicast_base (nullable): the allocation's NVLink-SHARP
+ *   all_gather:      out_r[this rank's runs] = in (local pointer)             (layer features of psi / o_t)
+ *   reduce_scatter:  out (local pointer) = sum_q in_q[this rank's runs]
+ * A rank's part of the gathered tensor is up to two runs [at0, at0 + len0) and [at1, at1 + len1) (floats,
+ * relative to out_off / in_off; the local buffer holds run 0 then run 1): equal blocks in rank order are
+ * {rank * block, block, 0, 0}; the node-sharded psi networks use two runs — the rank's source nodes and
+ * its target nodes in the natural [source ; target] order, so that no permutation is needed on either
+ * side.  max_len: the largest len0 + len1 over the ranks (every rank must launch the same grid).
+ * n, at*, len*, max_len in floats, multiples of 4.  multicast_base (nullable): the allocation's NVLink-SHARP
  * multicast mapping, if the fabric has one — the switch then does the additions (multimem.ld_reduce)
  * and the broadcast (multimem.st).
  * Handshakes: all_reduce opens ("all partials complete") and closes ("all results landed") with one.
@@ -303,9 +308,11 @@ size_t dgmc_sym_pad_bytes(void);
 int dgmc_sym_all_reduce(const void* const* peer_bases, const void* multicast_base, int rank, int world,
                         int64_t in_off, int64_t out_off, int64_t pad_off, int64_t n, dgmc_stream_t stream);
 int dgmc_sym_all_gather(const void* const* peer_bases, int rank, int world, const float* in, int64_t out_off,
-                        int64_t pad_off, int64_t block, int sync_before, dgmc_stream_t stream);
+                        int64_t pad_off, int64_t at0, int64_t len0, int64_t at1, int64_t len1, int64_t max_len,
+                        int sync_before, dgmc_stream_t stream);
 int dgmc_sym_reduce_scatter(const void* const* peer_bases, int rank, int world, int64_t in_off, float* out,
-                            int64_t pad_off, int64_t block, int sync_after, dgmc_stream_t stream);
+                            int64_t pad_off, int64_t at0, int64_t len0, int64_t at1, int64_t len1,
+                            int64_t max_len, int sync_after, dgmc_stream_t stream);
 /* number of handshakes that gave up so far on this device (synchronises the device); 0 in a healthy run */
 int dgmc_sym_timeouts(void);
 
