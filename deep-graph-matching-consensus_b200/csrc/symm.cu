@@ -109,24 +109,39 @@ __global__ void __launch_bounds__(SYM_THREADS) sym_all_reduce_kernel(const SymPe
                          ::"l"(dst + i), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
         }
     } else {
-        // four elements per thread and round: all peer loads of a round are in flight together
-        for (long long i0 = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < hi; i0 += 4 * stride) {
-            float4 acc[4];
+        // Peers are visited in the order rank + 1, rank + 2, ...: at any moment every rank reads from /
+        // writes to a DIFFERENT peer, so no GPU's NVLink ingress is hit by all the others at once.  The
+        // sum itself is taken in rank order 0, 1, ... (bit-identical results on every rank).
+        for (long long i = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += stride) {
+            float4 v[SYM_MAX_WORLD];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                const long long i = i0 + u * stride;
-                if (i < hi) {
-                    acc[u] = __ldcg(reinterpret_cast<const float4*>(p.base[0] + in_off) + i);
-                    for (int q = 1; q < world; ++q)
-                        acc[u] = add4(acc[u], __ldcg(reinterpret_cast<const float4*>(p.base[q] + in_off) + i));
+            for (int j = 0; j < SYM_MAX_WORLD; ++j) {
+                if (j < world) {
+                    int q = rank + 1 + j;
+                    if (q >= world) q -= world;
+                    v[j] = __ldcg(reinterpret_cast<const float4*>(p.base[q] + in_off) + i);
+                }
+            }
+            // v[j] belongs to rank (rank + 1 + j) % world, i.e. rank q sits at j = (q - rank - 1 + world) % world
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int q = 0; q < SYM_MAX_WORLD; ++q) {
+                if (q < world) {
+                    int j = q - rank - 1;
+                    if (j < 0) j += world;
+                    float4 t = v[0];
+#pragma unroll
+                    for (int u = 1; u < SYM_MAX_WORLD; ++u) if (u == j) t = v[u];
+                    acc = q == 0 ? t : add4(acc, t);
                 }
             }
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                const long long i = i0 + u * stride;
-                if (i < hi)
-                    for (int q = 0; q < world; ++q)
-                        __stcg(reinterpret_cast<float4*>(p.base[q] + out_off) + i, acc[u]);
+            for (int j = 0; j < SYM_MAX_WORLD; ++j) {
+                if (j < world) {
+                    int q = rank + 1 + j;
+                    if (q >= world) q -= world;
+                    __stcg(reinterpret_cast<float4*>(p.base[q] + out_off) + i, acc);
+                }
             }
         }
     }
@@ -155,8 +170,11 @@ __global__ void __launch_bounds__(SYM_THREADS) sym_all_gather_kernel(const SymPe
          i += (long long)gridDim.x * blockDim.x) {
         const float4 v = in[i];
         const long long j = runs.where(i);
-        for (int q = 0; q < world; ++q)
+        for (int u = 0; u < world; ++u) {     // staggered: see sym_all_reduce_kernel
+            int q = rank + 1 + u;
+            if (q >= world) q -= world;
             __stcg(reinterpret_cast<float4*>(p.base[q] + out_off) + j, v);
+        }
     }
     sym_block_barrier(p, pad_off, 1, rank, world);
 }
@@ -171,9 +189,27 @@ __global__ void __launch_bounds__(SYM_THREADS) sym_reduce_scatter_kernel(const S
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
          i += (long long)gridDim.x * blockDim.x) {
         const long long j = runs.where(i);
-        float4 acc = __ldcg(reinterpret_cast<const float4*>(p.base[0] + in_off) + j);
-        for (int q = 1; q < world; ++q)
-            acc = add4(acc, __ldcg(reinterpret_cast<const float4*>(p.base[q] + in_off) + j));
+        float4 v[SYM_MAX_WORLD];              // loads staggered over the peers, sum in rank order
+#pragma unroll
+        for (int u = 0; u < SYM_MAX_WORLD; ++u) {
+            if (u < world) {
+                int q = rank + 1 + u;
+                if (q >= world) q -= world;
+                v[u] = __ldcg(reinterpret_cast<const float4*>(p.base[q] + in_off) + j);
+            }
+        }
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int q = 0; q < SYM_MAX_WORLD; ++q) {
+            if (q < world) {
+                int u = q - rank - 1;
+                if (u < 0) u += world;
+                float4 t = v[0];
+#pragma unroll
+                for (int m = 1; m < SYM_MAX_WORLD; ++m) if (m == u) t = v[m];
+                acc = q == 0 ? t : add4(acc, t);
+            }
+        }
         out[i] = acc;
     }
     // closing handshake (peers have finished reading this rank's input): not needed when the caller

@@ -21,6 +21,8 @@ S, and the K1/K2/K3/K4/K6 kernels that touch them — exist only for the rank's 
 
 Results equal the single-GPU path up to the fp32 summation order of the all-reduce.
 """
+import copy
+
 import torch
 import torch.distributed as dist
 
@@ -49,8 +51,9 @@ def _peer(group, device, nbytes, numel):
     return PeerCollectives.of(group, device, nbytes)
 
 
-def _sum_over_ranks(x, group):
-    """-> a fresh tensor holding the sum of x over the ranks (x itself may be the peer scratch)."""
+def _sum_over_ranks(x, group, keep=True):
+    """-> the sum of x over the ranks (x itself may be the peer scratch); keep=False: the result may be
+    a view of the peer scratch that the caller consumes before its next collective."""
     pc = _peer(group, x.device, x.numel() * 4, x.numel()) if x.dtype == torch.float32 else None
     if pc is None:
         y = x.contiguous().clone()
@@ -60,24 +63,30 @@ def _sum_over_ranks(x, group):
     src = pc.scratch_in(1, n)
     if x.data_ptr() != src.data_ptr():       # the producer may already have written into the scratch
         src.copy_(x.reshape(1, n))
-    return pc.all_reduce(1, n).clone().view(x.shape)
+    y = pc.all_reduce(1, n)
+    return (y.clone() if keep else y).view(x.shape)
 
 
 class _AllReduceSum(torch.autograd.Function):
     """y = sum over ranks of x; the adjoint of a sum whose result every rank consumes in a
     replicated computation is again the sum of the ranks' gradients."""
     @staticmethod
-    def forward(ctx, x, group):
+    def forward(ctx, x, group, keep):
         ctx.group = group
-        return _sum_over_ranks(x, group)
+        return _sum_over_ranks(x, group, keep)
 
     @staticmethod
     def backward(ctx, g):
-        return _sum_over_ranks(g, ctx.group), None
+        return _sum_over_ranks(g, ctx.group), None, None
 
 
-def all_reduce_sum(x, group=None):
-    return _AllReduceSum.apply(x, group)
+def _scratch_in(group, device, rows, c):
+    pc = _peer(group, device, rows * c * 4, 4 * c)
+    return None if pc is None else pc.scratch_in(rows, c)
+
+
+def all_reduce_sum(x, group=None, keep=True):
+    return _AllReduceSum.apply(x, group, keep)
 
 
 def transport_partial_buffer(n_t, r, device, group):
@@ -197,7 +206,9 @@ class _AllGatherNodes(torch.autograd.Function):
         rows = runs[0][1] + runs[1][1]
         pc = _peer(group, g.device, g.numel() * 4, 4 * c) if g.dtype == torch.float32 else None
         if pc is not None:
-            pc.scratch_in(g.size(0), c).copy_(g)
+            src = pc.scratch_in(g.size(0), c)
+            if g.data_ptr() != src.data_ptr():      # the aggregation's backward may have written it there
+                src.copy_(g)
             return pc.reduce_scatter(rows, c, runs, max_rows), None, None, None, None
         zeros = g.new_zeros
         blocks = []
@@ -230,8 +241,13 @@ def sharded_relcnn(psi, x_full, sp, group, masks=None):
     feats = [torch.cat([x_full[sp.runs[0][0]:sp.runs[0][0] + sp.ns_loc],
                         x_full[sp.runs[1][0]:sp.runs[1][0] + sp.nt_loc]], dim=0)]
     full = x_full
+    # from the second layer on the aggregation's input is an all-gather, whose backward is a
+    # reduce-scatter of the aggregation's input gradient: that gradient is written straight into the
+    # buffer the reduce-scatter reads
+    rel_g = copy.copy(sp.rel)
+    rel_g.grad_buffer = lambda rows, c, device: _scratch_in(group, device, rows, c)
     for i, conv in enumerate(psi.convs):
-        stacked = ops.rel_aggregate_op(full, sp.rel)                      # [n_loc, 3 C]
+        stacked = ops.rel_aggregate_op(full, sp.rel if i == 0 else rel_g)    # [n_loc, 3 C]
         weight = ops.region_cached(('relconv', id(conv)), lambda c=conv: torch.cat(
             [c.root.weight, c.lin1.weight, c.lin2.weight], dim=1))
         h = ops.node_linear(stacked, weight, conv.root.bias, relu=True, key=('relconv', id(conv)))
@@ -355,7 +371,8 @@ class RowShardedDGMC(DGMC):
             r_s = torch.randn((1, N_s, R_in), dtype=h_t.dtype, device=h_t.device).view(N_s, R_in)
             # the partial transport goes straight into the buffer the peers' all-reduce kernels read
             part = transport_partial_buffer(N_t, R_in, h_t.device, self.group)
-            r_t = all_reduce_sum(ops.transport(S, r_s[lo:hi], cand, out=part), self.group)
+            # (r_t is consumed by the concatenation below before the next collective: no copy out)
+            r_t = all_reduce_sum(ops.transport(S, r_s[lo:hi], cand, out=part), self.group, keep=False)
             if sp is not None:
                 # node-sharded psi_2: every rank holds the layer-0 features of all nodes (r_s from the
                 # shared seed, the all-reduced r_t) and computes the layers for its own nodes

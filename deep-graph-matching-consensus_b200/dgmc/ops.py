@@ -789,8 +789,11 @@ class _RelAggregate(torch.autograd.Function):
         rel = ctx.rel
         g = _f32(g)
         c = g.size(1) // 3
+        # the node-sharded path hands in the buffer its reduce-scatter reads (no copy in between)
+        buf = getattr(rel, 'grad_buffer', None)
+        out = buf(rel.n_in, c, g.device) if buf is not None else None
         dx = segment_gather(g.view(3 * rel.n_out, c), rel.n_in, rel.b_src, ptr=rel.b_ptr, w=rel.b_w,
-                            seg_of=rel.b_seg)
+                            seg_of=rel.b_seg, out=out)
         return dx, None
 
 
