@@ -623,6 +623,47 @@ def sharded_parity(model, w, d, dev, rank, world):
     return result
 
 
+def scale_study(n, dev, rank, world, steps=3, warmup=2):
+    """BASELINE.json configs[4] in every bench line: one whole training step (forward + loss + backward +
+    Adam, issued eagerly: at this size the kernels are milliseconds long and a captured graph of the step
+    would not fit beside anything else) on an n x n-node pair — the same model, 5 edges per node, n / 4
+    training pairs — on the N GPUs of this run, max over ranks; at N > 1 with the parity check of the
+    headline workload.  The driver's scaling table divides these numbers across its N = 1, 2, 4, 8 runs."""
+    import torch.distributed as dist
+    w = dict(WORKLOAD, name='synthetic %d x %d-node pair' % (n, n), n_s=n, n_t=n, e_s=5 * n, e_t=5 * n,
+             train_pairs=n // 4)
+    host = make_inputs(w, seed=5)
+    d = {k: v.to(dev) for k, v in host.items()}
+    del host
+    model = build_model(w, dev, sharded=world > 1)
+    opt = torch.optim.Adam(model.parameters(), lr=1e-3, capturable=True)
+    torch.manual_seed(99)
+    for _ in range(warmup):
+        train_step(model, opt, d)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(steps):
+        loss = train_step(model, opt, d)
+    b.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([a.elapsed_time(b) / steps], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    out = {'workload': '%d x %d nodes, 300-d, RelCNN(300,256,L3)/RelCNN(64,64,L3), sparse k=10 (+10), 10 consensus '
+                       'steps, %d train pairs, 5 edges per node; eager step' % (n, n, n // 4),
+           'n_gpus': world, 'ms_per_step': ms.item(), 'steps_per_s': 1e3 / ms.item(), 'steps': steps,
+           'warmup': warmup, 'peak_memory_gb': round(torch.cuda.max_memory_allocated(dev) / 2 ** 30, 1)}
+    if world > 1:
+        out['parity'] = sharded_parity(model, w, d, dev, rank, world)
+    del model, opt, d, loss
+    sys.modules['dgmc.ops'].clear_caches()
+    torch.cuda.empty_cache()
+    return out
+
+
 def stage(msg):
     if os.environ.get('DGMC_BENCH_VERBOSE'):
         print('[bench rank %s] %s' % (os.environ.get('RANK', '0'), msg), file=sys.stderr, flush=True)
@@ -656,6 +697,8 @@ def main():
     ap.add_argument('--hot-kernels', action='store_true',
                     help='launch every hot kernel once inside the NVTX range "hot" and exit (for ncu --set full '
                          '--nvtx --nvtx-include "hot/"); with --scale-kernels N on the N x N pair')
+    ap.add_argument('--no-scale-study', action='store_true', help='skip the large-pair step of the bench line')
+    ap.add_argument('--scale-study-nodes', type=int, default=1000000, metavar='N')
     ap.add_argument('--no-roofline-1m', action='store_true', help='skip the 1M x 1M kernel sweep of the N=1 line')
     ap.add_argument('--profile-eager', action='store_true',
                     help='warm up, run --steps eager steps inside the NVTX range "timed_step" and exit '
@@ -841,6 +884,13 @@ def main():
     e2e_value = 1e3 / (ms2.item() / args.steps)
 
     stage('timing done')
+    study = None
+    if not args.nodes and not args.k and not args.no_scale_study:
+        del graphed, e2e_step
+        sys.modules['dgmc.ops'].clear_caches()
+        torch.cuda.empty_cache()
+        study = scale_study(args.scale_study_nodes, dev, rank, world)
+        stage('scale study done')
     if world > 1:  # all collective work is over: leave the group before rank 0's local epilogue
         dist.barrier()
         torch.cuda.synchronize()
@@ -899,9 +949,11 @@ def main():
         }
         if parity is not None:
             out['parity'] = parity
+        if study is not None:
+            out['scale_study'] = study
         if world == 1 and not args.nodes and not args.k and not args.no_roofline_1m:
             # BASELINE.json configs[4] shape, kernels alone: where HBM, not latency, is the roofline
-            del model, graphed, e2e_step
+            del model
             ops_mod = sys.modules['dgmc.ops']
             ops_mod.clear_caches()
             torch.cuda.empty_cache()
@@ -914,6 +966,8 @@ def main():
                 'value': sps, 'unit': 'steps/s', 'cores': cores, 'kind': kind,
                 'sample': '%d full step(s) of the same workload after 1 warm-up: %s; %.1f s/step' % (n, what, dt)}
         emit(out)
+    if world > 1 and rank == 0 and study is not None and not study['parity']['ok']:
+        parity = study['parity']
     if world > 1 and rank == 0 and parity is not None and not parity['ok']:
         print('bench: multi-GPU parity check FAILED: %s' % parity, file=sys.stderr, flush=True)
         store.set('dgmc_bench_done', '1')
