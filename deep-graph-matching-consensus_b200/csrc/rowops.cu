@@ -288,3 +288,75 @@ extern "C" int dgmc_gather_dot_fwd(const float* a, int64_t lda, const float* b, 
     }
     return check_launch("gather_dot_fwd");
 }
+
+// ---------------------------------------------------------------------------------------------
+// loss / acc / hits_at_k on the sparse side-cars (dgmc.py:246-311), one warp per ground-truth pair.
+// For pair g = (row, col): with v = val[row, :], c = idx[row, :]
+//   nll[g]     = sum_j [c_j == col] * -log(v_j + eps)        (dgmc.py:264-266: every listed copy counts)
+//   hits[g]    = #{j : c_j == col}                            (0: the pair is dropped from the mean)
+//   correct[g] = [c_{argmax v} == col]                        (first maximum, as torch.argmax; dgmc.py:281-284)
+//   in_top[g]  = #{j : c_j == col and v_j is among the top_k largest}   (stable order; dgmc.py:302-308)
+// The host sums the four arrays on the device; only the Python number the reference API returns
+// (`.item()`, dgmc.py:285,309) costs a synchronisation.
+// ---------------------------------------------------------------------------------------------
+namespace dgmc {
+__global__ void __launch_bounds__(256) sparse_metrics_kernel(const long long* __restrict__ idx,
+                                                             const float* __restrict__ val,
+                                                             const long long* __restrict__ y_row,
+                                                             const long long* __restrict__ y_col, long long pairs,
+                                                             int k, int top_k, float eps, float* __restrict__ nll,
+                                                             float* __restrict__ hits, float* __restrict__ correct,
+                                                             float* __restrict__ in_top) {
+    const int lane = threadIdx.x & 31;
+    const long long warps = (long long)gridDim.x * (blockDim.x >> 5);
+    for (long long g = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); g < pairs; g += warps) {
+        const long long row = y_row[g], col = y_col[g];
+        const long long* c = idx + row * k;
+        const float* v = val + row * k;
+        float my_nll = 0.f, my_hits = 0.f, my_top = 0.f;
+        float best = -INFINITY;
+        int best_j = k;
+        for (int j = lane; j < k; j += 32) {
+            const float vj = v[j];
+            if (vj > best) { best = vj; best_j = j; }        // ascending j per lane: first maximum kept
+            if (c[j] == col) {
+                my_nll += -logf(vj + eps);
+                my_hits += 1.f;
+                int rank = 0;                                 // entries that sort before j (descending, stable)
+                for (int i = 0; i < k; ++i) {
+                    const float vi = v[i];
+                    rank += (vi > vj) || (vi == vj && i < j);
+                }
+                my_top += rank < top_k ? 1.f : 0.f;
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+            const int oj = __shfl_xor_sync(0xffffffffu, best_j, o);
+            if (ob > best || (ob == best && oj < best_j)) { best = ob; best_j = oj; }
+        }
+        my_nll = warp_sum(my_nll);
+        my_hits = warp_sum(my_hits);
+        my_top = warp_sum(my_top);
+        if (lane == 0) {
+            nll[g] = my_nll;
+            hits[g] = my_hits;
+            correct[g] = (best_j < k && c[best_j] == col) ? 1.f : 0.f;
+            in_top[g] = my_top;
+        }
+    }
+}
+}  // namespace dgmc
+
+extern "C" int dgmc_sparse_metrics(const int64_t* idx, const float* val, const int64_t* y_row, const int64_t* y_col,
+                                   int64_t pairs, int k, int top_k, float eps, float* nll, float* hits,
+                                   float* correct, float* in_top, dgmc_stream_t stream) {
+    DGMC_REQUIRE(idx && val && y_row && y_col && nll && hits && correct && in_top && k >= 1 && pairs >= 0,
+                 "sparse_metrics: bad arguments");
+    if (pairs == 0) return DGMC_OK;
+    dgmc::sparse_metrics_kernel<<<dgmc::wave_grid(pairs, 8, 8), 256, 0, stream>>>(
+        reinterpret_cast<const long long*>(idx), val, reinterpret_cast<const long long*>(y_row),
+        reinterpret_cast<const long long*>(y_col), pairs, k, top_k, eps, nll, hits, correct, in_top);
+    return dgmc::check_launch("sparse_metrics");
+}

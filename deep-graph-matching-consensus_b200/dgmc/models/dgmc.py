@@ -262,6 +262,11 @@ class DGMC(torch.nn.Module):
             val = S[y[0], y[1]]
         else:
             assert S.__idx__ is not None and S.__val__ is not None
+            if reduction != 'none' and S.__val__.is_cuda and not (torch.is_grad_enabled() and
+                                                                   S.__val__.requires_grad):
+                # evaluation: one kernel over the ground-truth pairs, no gathers / masks
+                nll, hits, _, _ = ops.sparse_metrics(S.__idx__, S.__val__, y, eps=EPS)
+                return nll.sum() if reduction == 'sum' else nll.sum() / hits.sum()
             hit = S.__idx__[y[0]] == y[1].view(-1, 1)
             if reduction != 'none':
                 # same value as indexing with the boolean mask (every hit entry counts once,
@@ -281,6 +286,9 @@ class DGMC(torch.nn.Module):
             pred = S[y[0]].argmax(dim=-1)
         else:
             assert S.__idx__ is not None and S.__val__ is not None
+            if S.__val__.is_cuda:
+                correct = int(ops.sparse_metrics(S.__idx__, S.__val__, y)[2].sum().item())
+                return correct / y.size(1) if reduction == 'mean' else correct
             pred = S.__idx__[y[0], S.__val__[y[0]].argmax(dim=-1)]
         correct = (pred == y[1]).sum().item()
         return correct / y.size(1) if reduction == 'mean' else correct
@@ -292,6 +300,9 @@ class DGMC(torch.nn.Module):
             pred = S[y[0]].argsort(dim=-1, descending=True)[:, :k]
         else:
             assert S.__idx__ is not None and S.__val__ is not None
+            if S.__val__.is_cuda:
+                correct = int(ops.sparse_metrics(S.__idx__, S.__val__, y, top_k=k)[3].sum().item())
+                return correct / y.size(1) if reduction == 'mean' else correct
             order = S.__val__[y[0]].argsort(dim=-1, descending=True)[:, :k]
             pred = torch.gather(S.__idx__[y[0]], -1, order)
         correct = (pred == y[1].view(-1, 1)).sum().item()

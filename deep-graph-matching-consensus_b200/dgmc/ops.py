@@ -1089,6 +1089,22 @@ def spline_gather(y, base, graph, sb, n_kernels):
 
 
 # --------------------------------------------------------------------------------------------
+# loss / acc / hits_at_k on the sparse side-cars
+# --------------------------------------------------------------------------------------------
+def sparse_metrics(idx, val, y, top_k=1, eps=1e-8):
+    """One kernel over the ground-truth pairs y [2, G] of a sparse correspondence (idx int64 / val fp32
+    [rows, k]) -> device tensors (nll [G], hits [G], correct [G], in_top [G]); see dgmc_sparse_metrics."""
+    idx, val = idx.contiguous(), _f32(val.detach())
+    y_row, y_col = y[0].contiguous(), y[1].contiguous()
+    assert idx.dtype == torch.int64 and y_row.dtype == torch.int64 and idx.shape == val.shape
+    pairs = y_row.numel()
+    out = torch.zeros(4, max(pairs, 1), dtype=torch.float32, device=val.device)
+    call('dgmc_sparse_metrics', idx, val, y_row, y_col, pairs, idx.size(1), int(top_k), float(eps),
+         out[0], out[1], out[2], out[3], stream_ptr())
+    return out[0, :pairs], out[1, :pairs], out[2, :pairs], out[3, :pairs]
+
+
+# --------------------------------------------------------------------------------------------
 # dense branch
 # --------------------------------------------------------------------------------------------
 class _DenseConsensus(torch.autograd.Function):

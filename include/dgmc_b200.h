@@ -72,6 +72,17 @@ int dgmc_masked_softmax_fwd(const float* x, const uint8_t* s_mask, const uint8_t
 int dgmc_masked_softmax_bwd(const float* y, const float* dy, float* dx, int B, int n_s, int n_t,
                             dgmc_stream_t stream);
 
+/* ---- loss / acc / hits_at_k on the sparse side-cars, one pass ---------------------------------
+ * For every ground-truth pair g = (y_row[g], y_col[g]) over idx / val [rows, k] (int64 / fp32, the
+ * `__idx__` / `__val__` attributes of the sparse outputs):
+ *   nll[g] = sum over listed copies of -log(val + eps), hits[g] = number of copies (0: pair absent),
+ *   correct[g] = [idx at the row's first arg-max == y_col[g]], in_top[g] = copies among the top_k values.
+ * replaces the boolean-mask / argmax / argsort + gather chains of DGMC.loss / acc / hits_at_k
+ * (dgmc.py:262-266, 281-284, 302-308); the host adds the arrays up on the device. */
+int dgmc_sparse_metrics(const int64_t* idx, const float* val, const int64_t* y_row, const int64_t* y_col,
+                        int64_t pairs, int k, int top_k, float eps, float* nll, float* hits, float* correct,
+                        float* in_top, dgmc_stream_t stream);
+
 /* ---- K2: candidate gather-dot ---------------------------------------------------------
  * out[m, j] = < a[m, :], b[idx[m, j], :] >.  replaces gather + mul + sum at dgmc.py:198-201
  * (S_hat initialisation) and is the backward of the indicator transport (dS = <r_s, dr_t>).

@@ -392,3 +392,41 @@ def test_relcnn_direct_cat_matches_layerwise(lin, monkeypatch):
     assert len(gp1) == len(gp2)
     for a, b in zip(gp1, gp2):
         assert torch.allclose(a, b, rtol=1e-5, atol=1e-6 * b.abs().max().item())
+
+
+def test_sparse_metrics_kernel_matches_the_reference_formulas():
+    """loss / acc / hits_at_k on the side-cars in one kernel (dgmc_sparse_metrics) against the oracle's
+    restatement of dgmc.py:246-311, with the cases the reference formulas treat specially: ground truths
+    missing from the list (dropped from the mean), duplicated candidates (every copy counts)."""
+    from dgmc import ops
+    from dgmc.models import DGMC, GIN
+    from oracle import dgmc_oracle as O
+    g = torch.Generator().manual_seed(17)
+    rows, k, n_t, pairs = 500, 20, 300, 260
+    idx = torch.randint(n_t, (rows, k), generator=g)
+    idx[:, 5] = idx[:, 2]                                    # a duplicated candidate in every row
+    val = torch.rand(rows, k, generator=g).softmax(-1)       # distinct values: argsort order is unambiguous
+    y_row = torch.sort(torch.randperm(rows, generator=g)[:pairs])[0]
+    y_col = idx[y_row, torch.randint(k, (pairs, ), generator=g)]
+    y_col[::7] = (idx[y_row[::7]].max(dim=1)[0] + 1) % n_t   # some ground truths are not listed at all
+    y = torch.stack([y_row, y_col])
+    model = DGMC(GIN(4, 4, 1), GIN(4, 4, 1), num_steps=0, k=k)
+    S = torch.sparse_coo_tensor(torch.zeros(2, 0, dtype=torch.long), torch.zeros(0), (rows, n_t)).cuda()
+    S.__idx__, S.__val__ = idx.cuda(), val.cuda()
+    yc = y.cuda()
+    with torch.no_grad():
+        for red in ('mean', 'sum'):
+            assert torch.allclose(model.loss(S, yc, red).cpu(), O.loss(val, y, red, idx=idx), rtol=1e-5)
+    assert model.acc(S, yc) == pytest.approx(O.acc(val, y, idx=idx))
+    assert model.acc(S, yc, 'sum') == O.acc(val, y, 'sum', idx=idx)
+    for top in (1, 3, 10, 20):
+        assert model.hits_at_k(top, S, yc) == pytest.approx(O.hits_at_k(top, val, y, idx=idx)), top
+    nll, hits, correct, in_top = ops.sparse_metrics(S.__idx__, S.__val__, yc, top_k=k)
+    assert torch.equal(hits.cpu(), (idx[y_row] == y_col.view(-1, 1)).sum(1).float())
+    assert torch.equal(in_top, hits)                          # top_k = k: every listed copy is in
+    # with gradients the loss goes through differentiable ops and must agree with the kernel's value
+    S.__val__ = val.cuda().requires_grad_()
+    loss = model.loss(S, yc)
+    loss.backward()
+    assert torch.allclose(loss.detach().cpu(), O.loss(val, y, idx=idx), rtol=1e-5)
+    assert S.__val__.grad is not None
