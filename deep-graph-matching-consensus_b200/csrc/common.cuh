@@ -26,16 +26,34 @@ inline int check_launch(const char* what, int kernels = 1) {
     return DGMC_OK;
 }
 
-inline int sm_count() {
-    static int cached = 0;
-    if (!cached) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&cached, cudaDevAttrMultiProcessorCount, dev);
-        if (cached <= 0) cached = 148;
-    }
-    return cached;
+constexpr int MAX_DEVICES = 64;
+
+inline int current_device() {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    return (dev >= 0 && dev < MAX_DEVICES) ? dev : 0;
 }
+
+// SM count of the CURRENT device (cached per device: one process may drive several GPUs)
+inline int sm_count() {
+    static int cached[MAX_DEVICES] = {};
+    const int dev = current_device();
+    if (!cached[dev]) {
+        int n = 0;
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        cached[dev] = n > 0 ? n : 148;
+    }
+    return cached[dev];
+}
+
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is a per-DEVICE setting: a kernel configured on one
+// GPU is not configured on the next one this process uses.  One flag array per kernel instantiation:
+//   static DeviceOnce once;  if (!once.done()) { ...set the attribute...; once.mark(); }
+struct DeviceOnce {
+    bool flag[MAX_DEVICES] = {};
+    bool done() const { return flag[current_device()]; }
+    void mark() { flag[current_device()] = true; }
+};
 
 // cuTensorMapEncodeTiled is a DRIVER call and needs a current context on the calling thread.  A thread
 // that has not yet made a runtime call that binds the primary context (e.g. PyTorch's autograd worker

@@ -70,15 +70,28 @@ __global__ void __launch_bounds__(256) split_weight_kernel(const float* __restri
     }
 }
 
+// Dense-branch mode (DENSE = true): the batched score product S_hat[b] = h_s[b] h_t[b]^T of the dense
+// variant (dgmc.py:163) with the masked row softmax (dgmc.py:15-19,165) in the epilogue.  "X" = the
+// padded source embeddings [B n_s, C], "W" = the (split) padded target embeddings [B n_t, C]; tile t
+// covers the g graphs t g .. t g + g - 1 (g n_s <= 128 rows, g n_t <= 128 columns): rows t g n_s ..,
+// W rows t g n_t ...  Only the diagonal n_s x n_t blocks of the 128 x 128 tile are meaningful; the
+// tensor core computes the rest for free.  One epilogue thread = one row: it walks its graph's column
+// window three times (max, sum of exponentials, output) over TMEM and writes S_hat and S_0 itself.
+struct DenseArgs {
+    const uint8_t* s_mask; const uint8_t* t_mask;   // [B, n_s], [B, n_t]
+    float* s_hat; float* s_0;                       // [B, n_s, n_t]
+    int B, n_s, n_t, g;                             // g = graphs per tile
+};
+
 // LT_ACC: accumulator pairs [H | L] the k8 steps alternate between (2 for long reductions, see the
 // MMA issuer; 1 for k_in <= 128, which leaves room for a second accumulator set at BN = 128)
-template <int BN, int LT_ACC>
+template <int BN, int LT_ACC, bool DENSE>
 __global__ void __launch_bounds__(LT_THREADS, 1)
 linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_whi,
                  const __grid_constant__ CUtensorMap map_wlo, const __grid_constant__ CUtensorMap map_y,
                  int y_tma, const float* __restrict__ bias, long long bias_rows, int relu, float* __restrict__ y,
                  long long ldy,
-                 long long rows, int n_out, int k_blocks, int n_tiles_n, int n_tiles) {
+                 long long rows, int n_out, int k_blocks, int n_tiles_n, int n_tiles, const DenseArgs dense) {
     constexpr int B_BYTES = BN * LT_KB * 4;
     constexpr int STAGE_BYTES = 2 * LT_A_BYTES + 2 * B_BYTES;
     constexpr int NSTAGE = lt_stages(BN);
@@ -126,7 +139,8 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
             // ================= TMA producer =================
             int s = 0; uint32_t phase = 0;
             for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-                const int m0 = (tile / n_tiles_n) * LT_BM, n0 = (tile % n_tiles_n) * BN;
+                const int m0 = DENSE ? tile * dense.g * dense.n_s : (tile / n_tiles_n) * LT_BM;
+                const int n0 = DENSE ? tile * dense.g * dense.n_t : (tile % n_tiles_n) * BN;
                 for (int kb = 0; kb < k_blocks; ++kb) {
                     mbar_wait(&empty[s], phase ^ 1u);
                     uint8_t* st = smem + (size_t)s * STAGE_BYTES;
@@ -215,6 +229,75 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
             const int n0 = (tile % n_tiles_n) * BN;
             mbar_wait(&acc_full[buf], (uint32_t)(use & 1));
             tcgen05_fence_after();
+            if (DENSE) {
+                // ---- masked row softmax of this row's n_s x n_t block, straight out of TMEM ----
+                const int r = quarter * 32 + lane;                 // row of the tile
+                const int gi = r / dense.n_s, i = r - gi * dense.n_s;
+                const int b = tile * dense.g + gi;
+                const bool valid = gi < dense.g && b < dense.B;
+                const int w0 = gi * dense.n_t;                     // first column of the graph's window
+                const bool on = valid && dense.s_mask[(size_t)b * dense.n_s + i] != 0;
+                const uint8_t* tm = dense.t_mask + (size_t)(valid ? b : 0) * dense.n_t;
+                const uint32_t lane_base0 = tmem_d + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * ACC_COLS);
+                auto chunk = [&](int cb, float (&v)[32]) {         // v = (H_0 + H_1) + (L_0 + L_1)
+                    const uint32_t lane_base = lane_base0 + (uint32_t)cb;
+                    float l[32];
+                    tmem_ld_32x32b_x32_pair(lane_base, lane_base + (uint32_t)BN, v, l);
+                    if (LT_ACC == 2) {
+                        float q[32], m[32];
+                        tmem_ld_32x32b_x32_pair(lane_base + (uint32_t)(2 * BN), lane_base + (uint32_t)(3 * BN), q, m);
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) { v[j] += q[j]; l[j] += m[j]; }
+                    }
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] += l[j];
+                };
+                float mx = -INFINITY, sum = 0.f;
+#pragma unroll 1
+                for (int cb = 0; cb < BN; cb += 32) {              // pass 1: row maximum over the live columns
+                    float v[32];
+                    chunk(cb, v);
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const int col = cb + j - w0;
+                        if (on && col >= 0 && col < dense.n_t && tm[col]) mx = fmaxf(mx, v[j]);
+                    }
+                }
+#pragma unroll 1
+                for (int cb = 0; cb < BN; cb += 32) {              // pass 2: sum of exponentials
+                    float v[32];
+                    chunk(cb, v);
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const int col = cb + j - w0;
+                        if (on && col >= 0 && col < dense.n_t && tm[col]) sum += __expf(v[j] - mx);
+                    }
+                }
+                const float inv = sum > 0.f ? 1.f / sum : 0.f;
+#pragma unroll 1
+                for (int cb = 0; cb < BN; cb += 32) {              // pass 3: S_hat and S_0
+                    float v[32];
+                    chunk(cb, v);
+                    if (cb + 32 >= BN) {                           // last TMEM read of this accumulator set
+                        tcgen05_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(&acc_empty[buf]);
+                    }
+                    if (valid) {
+                        float* sh = dense.s_hat + ((size_t)b * dense.n_s + i) * dense.n_t;
+                        float* s0 = dense.s_0 + ((size_t)b * dense.n_s + i) * dense.n_t;
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            const int col = cb + j - w0;
+                            if (col >= 0 && col < dense.n_t) {
+                                sh[col] = v[j];
+                                s0[col] = (on && tm[col]) ? __expf(v[j] - mx) * inv : 0.f;
+                            }
+                        }
+                    }
+                }
+                continue;
+            }
             const long long row0 = m0 + quarter * 32, row = row0 + lane;
 #pragma unroll 1
             for (int cb = 0; cb < BN; cb += 32) {
@@ -328,24 +411,26 @@ template <int BN, int ACC>
 static int lt_launch(const CUtensorMap& mx, const CUtensorMap& mh, const CUtensorMap& ml,
                      const CUtensorMap& my, int y_tma, const float* bias, long long bias_rows, int relu, float* y, long long ldy, long long rows, int n_out, int k_blocks, int n_pad,
                      cudaStream_t stream) {
+    const DenseArgs no_dense = {};
     constexpr int STAGE = 2 * LT_A_BYTES + 2 * BN * LT_KB * 4;
     // the full ring always (>= 192 KB): one CTA per SM, which owns all 512 TMEM columns
     const size_t smem = (size_t)lt_stages(BN) * STAGE + 4 * LT_OUT_BYTES + (3 * LT_MAX_STAGES + 6) * 8 + 1024;
-    static bool configured = false;
-    if (!configured) {
-        if (cudaFuncSetAttribute(linear_tc_kernel<BN, ACC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    static DeviceOnce configured;
+    if (!configured.done()) {
+        if (cudaFuncSetAttribute(linear_tc_kernel<BN, ACC, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)smem) != cudaSuccess) {
             set_error("linear_tc: cannot set %zu bytes of dynamic shared memory", smem);
             return DGMC_ERR_CUDA;
         }
-        configured = true;
+        configured.mark();
     }
     const int n_tiles_n = n_pad / BN;
     const long long tiles = (long long)n_tiles_n * ((rows + LT_BM - 1) / LT_BM);
     if (tiles > 0x7fffffffLL) { set_error("linear_tc: too many tiles"); return DGMC_ERR_UNSUPPORTED; }
     const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
-    linear_tc_kernel<BN, ACC><<<grid, LT_THREADS, smem, stream>>>(mx, mh, ml, my, y_tma, bias, bias_rows, relu, y, ldy, rows,
-                                                            n_out, k_blocks, n_tiles_n, (int)tiles);
+    linear_tc_kernel<BN, ACC, false><<<grid, LT_THREADS, smem, stream>>>(mx, mh, ml, my, y_tma, bias, bias_rows, relu, y,
+                                                                   ldy, rows, n_out, k_blocks, n_tiles_n, (int)tiles,
+                                                                   no_dense);
     return DGMC_OK;
 }
 
@@ -428,4 +513,70 @@ extern "C" int dgmc_linear_tc_rows(const float* x, int64_t ldx, const void* spli
                                    int k_in, dgmc_stream_t stream) {
     DGMC_REQUIRE(bias_rows >= 0 && bias_rows <= rows, "linear_tc_rows: bias_rows out of range");
     return linear_tc_impl(x, ldx, split_weight, bias, bias_rows, relu, y, ldy, rows, n_out, k_in, stream);
+}
+
+// ---- dense branch: S_hat = h_s h_t^T per graph + masked row softmax ---------------------------------
+extern "C" int dgmc_dense_scores_tc_supported(int B, int n_s, int n_t, int c, const float* h_s, const float* h_t) {
+    return B >= 1 && n_s >= 1 && n_s <= tc::LT_BM && n_t >= 1 && n_t <= 128 && c >= 1 && c % 4 == 0 &&
+           (long long)B * (n_s > n_t ? n_s : n_t) < (1LL << 30) &&
+           ((reinterpret_cast<uintptr_t>(h_s) | reinterpret_cast<uintptr_t>(h_t)) & 15) == 0;
+}
+
+extern "C" size_t dgmc_dense_scores_tc_workspace(int B, int n_t, int c) {
+    if (B < 1 || n_t < 1 || c < 1) return 0;
+    const size_t n_pad = tc::lt_round(B * n_t, 128), k_pad = tc::lt_round(c, tc::LT_KB);
+    return 2 * n_pad * k_pad * sizeof(float);
+}
+
+extern "C" int dgmc_dense_scores_tc(const float* h_s, const float* h_t, const uint8_t* s_mask, const uint8_t* t_mask,
+                                    float* s_hat, float* s_0, int B, int n_s, int n_t, int c, void* workspace,
+                                    size_t workspace_bytes, dgmc_stream_t stream) {
+    DGMC_REQUIRE(h_s && h_t && s_mask && t_mask && s_hat && s_0 && workspace, "dense_scores_tc: null argument");
+    if (!dgmc_dense_scores_tc_supported(B, n_s, n_t, c, h_s, h_t)) {
+        set_error("dense_scores_tc: unsupported shape (B=%d n_s=%d n_t=%d c=%d; graphs of up to 128 nodes, c %% 4 == 0, "
+                  "16-byte aligned embeddings)", B, n_s, n_t, c);
+        return DGMC_ERR_UNSUPPORTED;
+    }
+    DGMC_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 127) == 0, "dense_scores_tc: workspace must be 128-byte aligned");
+    if (workspace_bytes < dgmc_dense_scores_tc_workspace(B, n_t, c)) {
+        set_error("dense_scores_tc: workspace too small");
+        return DGMC_ERR_WORKSPACE;
+    }
+    // 1. split h_t (the "weight" operand: [B n_t, c]) into tf32 hi / lo, K-major, zero-padded
+    const int n_rows_t = B * n_t;
+    const int n_pad = tc::lt_round(n_rows_t, 128), k_pad = tc::lt_round(c, tc::LT_KB);
+    float* hi = static_cast<float*>(workspace);
+    float* lo = hi + (size_t)n_pad * k_pad;
+    {
+        const long long total = (long long)n_pad * k_pad;
+        int blocks = (int)((total + 255) / 256);
+        if (blocks > 8 * sm_count()) blocks = 8 * sm_count();
+        tc::split_weight_kernel<<<blocks, 256, 0, stream>>>(h_t, c, 0, n_rows_t, c, n_pad, k_pad, hi, lo);
+        if (int e = check_launch("dense_scores_tc (split)")) return e;
+    }
+    // 2. one 128 x 128 tile per g graphs
+    const int g_s = tc::LT_BM / n_s, g_t = 128 / n_t;
+    tc::DenseArgs d;
+    d.s_mask = s_mask; d.t_mask = t_mask; d.s_hat = s_hat; d.s_0 = s_0;
+    d.B = B; d.n_s = n_s; d.n_t = n_t; d.g = g_s < g_t ? g_s : g_t;
+    const int tiles = (B + d.g - 1) / d.g;
+    CUtensorMap mx, mh, ml;
+    if (int e = tc::lt_make_map(&mx, h_s, (long long)B * n_s, c, c, tc::LT_BM)) return e;
+    if (int e = tc::lt_make_map(&mh, hi, n_pad, k_pad, k_pad, 128)) return e;
+    if (int e = tc::lt_make_map(&ml, lo, n_pad, k_pad, k_pad, 128)) return e;
+    constexpr int STAGE = 2 * tc::LT_A_BYTES + 2 * 128 * tc::LT_KB * 4;
+    const size_t smem = (size_t)tc::lt_stages(128) * STAGE + 4 * tc::LT_OUT_BYTES + (3 * tc::LT_MAX_STAGES + 6) * 8 + 1024;
+    static DeviceOnce configured;
+    if (!configured.done()) {
+        if (cudaFuncSetAttribute(tc::linear_tc_kernel<128, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)smem) != cudaSuccess) {
+            set_error("dense_scores_tc: cannot set %zu bytes of dynamic shared memory", smem);
+            return DGMC_ERR_CUDA;
+        }
+        configured.mark();
+    }
+    const int grid = tiles < sm_count() ? tiles : sm_count();
+    tc::linear_tc_kernel<128, 2, true><<<grid, tc::LT_THREADS, smem, stream>>>(
+        mx, mh, ml, mx, 0, nullptr, 0, 0, nullptr, 0, (long long)B * n_s, 128, k_pad / tc::LT_KB, 1, tiles, d);
+    return check_launch("dense_scores_tc");
 }

@@ -492,16 +492,14 @@ extern "C" int dgmc_relconv_tc(const int32_t* ptr, const int32_t* src, const flo
     if (int e = tc::rc_make_map(&mx, x, rows, c, ldx, tc::RC_BM)) return e;
     if (int e = tc::rc_make_map(&mh, hi, n_pad, k_pad, k_pad, tc::RC_BN)) return e;
     if (int e = tc::rc_make_map(&ml, lo, n_pad, k_pad, k_pad, tc::RC_BN)) return e;
-    int dev = 0;
-    cudaGetDevice(&dev);
-    static bool configured[64] = {};
-    if (dev >= 0 && dev < 64 && !configured[dev]) {
+    static DeviceOnce configured;
+    if (!configured.done()) {
         if (cudaFuncSetAttribute(tc::relconv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)tc::RC_SMEM) != cudaSuccess) {
             set_error("relconv_tc: cannot set %zu bytes of dynamic shared memory", tc::RC_SMEM);
             return DGMC_ERR_CUDA;
         }
-        configured[dev] = true;
+        configured.mark();
     }
     tc::RelConvArgs a;
     a.ptr = ptr; a.src = src; a.w = w; a.order = order; a.x = x; a.ldx = ldx; a.stacked = stacked; a.lds = lds;

@@ -445,7 +445,8 @@ static Plan make_plan(int n_s, int n_t, int c, int k) {
 template <int KP, int MH>
 static int launch_main(const Plan& p, const CUtensorMap& ma, const CUtensorMap& mb, const MainArgs& args,
                        cudaStream_t stream) {
-    static size_t configured = 0;
+    static size_t configured_on[MAX_DEVICES] = {};      // per device: the attribute is a per-device setting
+    size_t& configured = configured_on[current_device()];
     if (p.smem > configured) {
         if (cudaFuncSetAttribute(topk_tc_kernel<KP, MH>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)p.smem) != cudaSuccess) {

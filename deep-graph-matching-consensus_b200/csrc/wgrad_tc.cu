@@ -284,14 +284,14 @@ template <int BN>
 static int wt_launch(const CUtensorMap& mx, const CUtensorMap& mg, long long K, int M, int N, int splits,
                      long long bias_rows, float* partial, float* partial_b, cudaStream_t stream) {
     const size_t smem = wt_smem(BN);
-    static bool configured = false;
-    if (!configured) {
+    static DeviceOnce configured;
+    if (!configured.done()) {
         if (cudaFuncSetAttribute(wgrad_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)smem) != cudaSuccess) {
             set_error("wgrad_tc_partial: cannot set %zu bytes of dynamic shared memory", smem);
             return DGMC_ERR_CUDA;
         }
-        configured = true;
+        configured.mark();
     }
     dim3 grid((N + WT_TN - 1) / WT_TN, splits);
     wgrad_tc_kernel<BN><<<grid, WT_THREADS, smem, stream>>>(mx, mg, K, M, N, splits, wt_stages(BN), bias_rows, partial, partial_b);

@@ -12,6 +12,8 @@ and the per-node library GEMMs.  Everything index-driven or row-wise is a kernel
   dgmc.py:202..225 softmax over k       -> K3  ops.softmax_k / ops.masked_softmax
   dgmc.py:209-212  scatter_add          -> K4  ops.transport         (by-target CSR gather)
   dgmc.py:219-223  gather, sub, mlp(D)  -> K6  ops.diff_mlp          (first Linear hoisted)
+  dgmc.py:163-165  h_s h_t^T + softmax  ->     ops.dense_scores      (tcgen05, softmax in the epilogue)
+  dgmc.py:170      S^T r_s (dense)      ->     ops.dense_transport   (small batched products)
   dgmc.py:178-179  dense D and mlp(D)   ->     ops.dense_consensus
 
 There is no CPU path: CPU tensors raise `DgmcNativeError`.
@@ -200,12 +202,20 @@ class DGMC(torch.nn.Module):
                 else s_mask.to(torch.uint8)
             tm = torch.ones(B, N_t, dtype=torch.uint8, device=h_s.device) if t_mask is None \
                 else t_mask.to(torch.uint8)
-            S_hat = h_s @ h_t.transpose(-1, -2)
-            S_0 = _rows(ops.masked_softmax(S_hat, sm, tm), s_mask)
-            for _ in range(num_steps):
+            small = ops.dense_scores_ok(h_s, h_t)
+            if small:
+                # graphs of up to 128 nodes (every reference configuration): scores on the tensor cores
+                # with the masked softmax in the epilogue, transport as small exact-fp32 batched products
+                S_hat, S = ops.dense_scores(h_s, h_t, sm, tm)
+            else:
+                S_hat = h_s @ h_t.transpose(-1, -2)
                 S = ops.masked_softmax(S_hat, sm, tm)
+            S_0 = _rows(S, s_mask)
+            for step in range(num_steps):
+                if step > 0:
+                    S = ops.masked_softmax(S_hat, sm, tm)
                 r_s = torch.randn((B, N_s, R_in), dtype=h_s.dtype, device=h_s.device)
-                r_t = S.transpose(-1, -2) @ r_s
+                r_t = ops.dense_transport(S, r_s) if small else S.transpose(-1, -2) @ r_s
                 p_s, p_t = consensus_nodes(r_s, r_t)
                 S_hat = ops.dense_consensus(S_hat, p_s.view(B, N_s, -1), p_t.view(B, N_t, -1), w2,
                                             b2, sm, tm)

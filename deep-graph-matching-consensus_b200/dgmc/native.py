@@ -120,11 +120,26 @@ def stream_ptr():
 LAUNCHES = [0]  # number of native entry points called (bench.py reports it as gpu_launches)
 
 
+def _device_of(a):
+    t = a.t if isinstance(a, RowStrided) else a
+    return t.device if torch.is_tensor(t) and t.is_cuda else None
+
+
 def call(name, *args):
-    """Call an `int dgmc_*` entry point; tensors become device pointers; raises on failure."""
+    """Call an `int dgmc_*` entry point; tensors become device pointers; raises on failure.  The
+    kernels run on the CURRENT device and stream: tensors that live on another GPU are an error (wrap
+    the call in `torch.cuda.device(tensor.device)`), not a launch on the wrong device."""
     fn = getattr(lib, name)
     conv = [_ptr(a) if (a is None or torch.is_tensor(a) or isinstance(a, RowStrided)) else a
             for a in args]
+    for a in args:
+        dev = _device_of(a)
+        if dev is not None:
+            if dev.index != torch.cuda.current_device():
+                raise DgmcNativeError('%s: tensor on %s but the current device is cuda:%d; use '
+                                      'torch.cuda.set_device / torch.cuda.device(...)' %
+                                      (name, dev, torch.cuda.current_device()))
+            break    # torch ops already require all tensors of a call on one device
     LAUNCHES[0] += 1
     rc = fn(*conv)
     if rc != 0:

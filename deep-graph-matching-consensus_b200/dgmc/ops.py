@@ -1107,6 +1107,94 @@ def sparse_metrics(idx, val, y, top_k=1, eps=1e-8):
 # --------------------------------------------------------------------------------------------
 # dense branch
 # --------------------------------------------------------------------------------------------
+def _bmm_nn(a, bm, trans_a=False):
+    """out[b] = op(a[b]) @ bm[b] for small per-graph matrices (dgmc_small_bmm_nn), exact fp32."""
+    a, bm = _f32(a), _f32(bm)
+    batch = a.size(0)
+    m, k = (a.size(2), a.size(1)) if trans_a else (a.size(1), a.size(2))
+    n = bm.size(2)
+    assert bm.size(1) == k and bm.size(0) == batch
+    out = torch.empty(batch, m, n, dtype=torch.float32, device=a.device)
+    call('dgmc_small_bmm_nn', a, int(trans_a), bm, out, batch, m, k, n, stream_ptr())
+    return out
+
+
+def _bmm_nt(a, bm):
+    """out[b] = a[b] @ bm[b]^T  (a [B, m, k], bm [B, n, k])."""
+    a, bm = _f32(a), _f32(bm)
+    batch, m, k = a.shape
+    n = bm.size(1)
+    out = torch.empty(batch, m, n, dtype=torch.float32, device=a.device)
+    call('dgmc_small_bmm_nt', a, bm, out, batch, m, n, k, stream_ptr())
+    return out
+
+
+def dense_small_ok(n_s, n_t):
+    return n_s <= 128 and n_t <= 128
+
+
+class _DenseTransport(torch.autograd.Function):
+    """r_t = S^T r_s per graph (dgmc.py:170): S [B, N_s, N_t], r_s [B, N_s, R] -> [B, N_t, R]."""
+    @staticmethod
+    def forward(ctx, S, r_s):
+        ctx.save_for_backward(S, r_s)
+        return _bmm_nn(S, r_s, trans_a=True)
+
+    @staticmethod
+    def backward(ctx, g):
+        S, r_s = ctx.saved_tensors
+        dS = _bmm_nt(r_s, g) if ctx.needs_input_grad[0] else None        # dS[i, j] = <r_s[i], g[j]>
+        dr = _bmm_nn(S, g) if ctx.needs_input_grad[1] else None           # dr_s = S g
+        return dS, dr
+
+
+def dense_transport(S, r_s):
+    return _DenseTransport.apply(S, r_s)
+
+
+class _DenseScores(torch.autograd.Function):
+    """(S_hat, S_0) = (h_s h_t^T, masked_softmax(S_hat)) per graph (dgmc.py:163-165) on the tensor cores
+    (dgmc_dense_scores_tc); adjoints through the small batched products."""
+    @staticmethod
+    def forward(ctx, h_s, h_t, sm, tm):
+        h_s, h_t = _f32(h_s), _f32(h_t)
+        B, n_s, c = h_s.shape
+        n_t = h_t.size(1)
+        s_hat = torch.empty(B, n_s, n_t, dtype=torch.float32, device=h_s.device)
+        s_0 = torch.empty_like(s_hat)
+        ws = _workspace(query('dgmc_dense_scores_tc_workspace', B, n_t, c) + 128, h_s.device)
+        ws = ws[(-ws.data_ptr()) % 128:]
+        call('dgmc_dense_scores_tc', h_s, h_t, sm, tm, s_hat, s_0, B, n_s, n_t, c, ws, ws.numel(), stream_ptr())
+        ctx.save_for_backward(h_s, h_t, s_0)
+        return s_hat, s_0
+
+    @staticmethod
+    def backward(ctx, g_hat, g_0):
+        h_s, h_t, s_0 = ctx.saved_tensors
+        B, n_s, n_t = s_0.shape
+        g = None
+        if g_0 is not None:   # through the softmax: dx = y (dy - <y, dy>), zero outside the mask
+            g = torch.empty_like(s_0)
+            call('dgmc_masked_softmax_bwd', s_0, _f32(g_0), g, B, n_s, n_t, stream_ptr())
+        if g_hat is not None:
+            g = _f32(g_hat) if g is None else g + g_hat
+        if g is None:
+            return None, None, None, None
+        d_hs = _bmm_nn(g, h_t) if ctx.needs_input_grad[0] else None                    # dS h_t
+        d_ht = _bmm_nn(g, h_s, trans_a=True) if ctx.needs_input_grad[1] else None      # dS^T h_s
+        return d_hs, d_ht, None, None
+
+
+def dense_scores_ok(h_s, h_t):
+    B, n_s, c = h_s.shape
+    return h_s.is_cuda and h_s.dtype == torch.float32 and dense_small_ok(n_s, h_t.size(1)) and c % 4 == 0
+
+
+def dense_scores(h_s, h_t, sm, tm):
+    """-> (S_hat, S_0) of the dense variant; h_s [B, N_s, C], h_t [B, N_t, C] zero-padded batches, masks uint8."""
+    return _DenseScores.apply(h_s.contiguous(), h_t.contiguous(), sm, tm)
+
+
 class _DenseConsensus(torch.autograd.Function):
     @staticmethod
     def forward(ctx, s_hat, ps, pt, w2, b2, sm, tm):

@@ -273,6 +273,29 @@ int dgmc_relconv_tc(const int32_t* ptr, const int32_t* src, const float* w, cons
                     float* stacked, int64_t lds, float* y, int64_t ldy, int64_t rows, int c, int n_out,
                     dgmc_stream_t stream);
 
+/* ---- dense branch: correspondence scores + masked row softmax on the tensor cores -------------------
+ * s_hat[b] = h_s[b] h_t[b]^T, s_0[b] = masked_softmax(s_hat[b]) with S_mask = s_mask (x) t_mask.
+ * replaces `h_s @ h_t.transpose(-1, -2)` and masked_softmax at dgmc.py:163-165 (ATen bmm + softmax).
+ * The dgmc_linear_tc kernel in block-diagonal mode: tcgen05 kind::tf32 with hi/lo splitting (fp32-level),
+ * one 128 x 128 tile per group of graphs, the softmax in the epilogue straight out of TMEM.  h_s
+ * [B, n_s, c], h_t [B, n_t, c] zero-padded batches; graphs of up to 128 nodes, c % 4 == 0.  The
+ * workspace receives the split copy of h_t. */
+int dgmc_dense_scores_tc_supported(int B, int n_s, int n_t, int c, const float* h_s, const float* h_t);
+size_t dgmc_dense_scores_tc_workspace(int B, int n_t, int c);
+int dgmc_dense_scores_tc(const float* h_s, const float* h_t, const uint8_t* s_mask, const uint8_t* t_mask,
+                         float* s_hat, float* s_0, int B, int n_s, int n_t, int c, void* workspace,
+                         size_t workspace_bytes, dgmc_stream_t stream);
+
+/* ---- dense branch: batched products of small per-graph matrices (exact fp32) ------------------------
+ * nn: out[b] [m, n] = op(a[b]) [m, k] * bm[b] [k, n], op = transpose when trans_a (a[b] stored [k, m]);
+ * nt: out[b] [m, n] = a[b] [m, k] * bm[b]^T (bm[b] stored [n, k]).  m, k <= 128 (nn).
+ * replaces ATen bmm for r_t = S^T r_s (dgmc.py:170) and for the adjoints of that product and of the
+ * score product (dS = r_s g^T, dr_s = S g, dh_s = dS h_t, dh_t = dS^T h_s). */
+int dgmc_small_bmm_nn(const float* a, int trans_a, const float* bm, float* out, int batch, int m, int k, int n,
+                      dgmc_stream_t stream);
+int dgmc_small_bmm_nt(const float* a, const float* bm, float* out, int batch, int m, int n, int k,
+                      dgmc_stream_t stream);
+
 /* ---- dense branch: consensus update without materialising D [B, N_s, N_t, R] ----------------
  * s_out[b,i,j] = s_in[b,i,j] + [s_mask[b,i] & t_mask[b,j]] * (b2 + sum_c w2[c] relu(ps[b,i,c] - pt[b,j,c]))
  * replaces D = o_s[:, :, None] - o_t[:, None], mlp(D).masked_fill(~S_mask, 0) at dgmc.py:178-179

@@ -430,3 +430,56 @@ def test_sparse_metrics_kernel_matches_the_reference_formulas():
     loss.backward()
     assert torch.allclose(loss.detach().cpu(), O.loss(val, y, idx=idx), rtol=1e-5)
     assert S.__val__.grad is not None
+
+
+@pytest.mark.parametrize('B,n_s,n_t,c', [(512, 20, 20, 256), (1, 100, 100, 64), (3, 7, 5, 8), (5, 128, 128, 32),
+                                          (70, 17, 23, 36), (2, 128, 3, 300)])
+def test_dense_scores_tensor_core_matches_fp64(B, n_s, n_t, c):
+    """S_hat = h_s h_t^T and S_0 = masked_softmax(S_hat) (dgmc.py:163-165) from the block-diagonal
+    tcgen05 kernel against fp64, ragged masks, and the adjoints through the small batched products.
+    Tolerance: fp32 level (3xTF32) — 2e-6 of the largest score, 1e-5 relative on S_0 (+1e-7)."""
+    from dgmc import ops
+    g = torch.Generator().manual_seed(B + n_s + c)
+    sizes_s = torch.randint(max(1, n_s // 2), n_s + 1, (B, ), generator=g)
+    sizes_t = torch.randint(max(1, n_t // 2), n_t + 1, (B, ), generator=g)
+    sizes_s[0], sizes_t[0] = n_s, n_t
+    sm = (torch.arange(n_s).view(1, -1) < sizes_s.view(-1, 1))
+    tm = (torch.arange(n_t).view(1, -1) < sizes_t.view(-1, 1))
+    h_s = torch.randn(B, n_s, c, generator=g) * sm.unsqueeze(-1)          # padded rows are zero (to_dense_batch)
+    h_t = torch.randn(B, n_t, c, generator=g) * tm.unsqueeze(-1)
+    g_hat, g_0 = torch.randn(B, n_s, n_t, generator=g), torch.randn(B, n_s, n_t, generator=g)
+
+    def ref(dtype):
+        a, b = h_s.to(dtype).requires_grad_(), h_t.to(dtype).requires_grad_()
+        s_hat = a @ b.transpose(-1, -2)
+        mask = sm.unsqueeze(2) & tm.unsqueeze(1)
+        s_0 = s_hat.masked_fill(~mask, float('-inf')).softmax(-1).masked_fill(~mask, 0)
+        s_0 = torch.nan_to_num(s_0, nan=0.0)
+        ((s_hat * g_hat.to(dtype)).sum() + (s_0 * g_0.to(dtype)).sum()).backward()
+        return s_hat.detach(), s_0.detach(), a.grad, b.grad
+
+    r = ref(torch.float64)
+    a, b = h_s.cuda().requires_grad_(), h_t.cuda().requires_grad_()
+    assert ops.dense_scores_ok(a, b)
+    s_hat, s_0 = ops.dense_scores(a, b, sm.cuda().to(torch.uint8), tm.cuda().to(torch.uint8))
+    ((s_hat * g_hat.cuda()).sum() + (s_0 * g_0.cuda()).sum()).backward()
+    scale = r[0].abs().max().item()
+    assert (s_hat.detach().double().cpu() - r[0]).abs().max().item() <= 2e-6 * scale
+    err0 = (s_0.detach().double().cpu() - r[1]).abs()
+    assert bool((err0 <= 1e-5 * r[1].abs() + 4e-6 * scale * r[1].abs() + 1e-7).all())   # d softmax = S * d logit
+    for got, want in ((a.grad, r[2]), (b.grad, r[3])):
+        assert (got.double().cpu() - want).abs().max().item() <= 1e-5 * want.abs().max().item()
+
+
+def test_small_batched_products_match_bmm():
+    from dgmc import ops
+    g = torch.Generator().manual_seed(4)
+    for B, m, k, n in ((512, 20, 20, 128), (3, 100, 100, 32), (7, 5, 128, 6), (2, 128, 9, 301)):
+        a = torch.randn(B, m, k, generator=g).cuda()
+        at = torch.randn(B, k, m, generator=g).cuda()
+        bm = torch.randn(B, k, n, generator=g).cuda()
+        bt = torch.randn(B, n, k, generator=g).cuda()
+        for got, want in ((ops._bmm_nn(a, bm), a.double() @ bm.double()),
+                          (ops._bmm_nn(at, bm, trans_a=True), at.double().transpose(1, 2) @ bm.double()),
+                          (ops._bmm_nt(a, bt), a.double() @ bt.double().transpose(1, 2))):
+            assert (got.double() - want).abs().max().item() <= 2e-6 * want.abs().max().item() * max(1, k ** 0.5)
