@@ -497,14 +497,19 @@ def pascal_step_bench(dev, steps, warmup):
             off += n
         return [t.to(dev) for t in (torch.cat(xs), torch.cat(es, 1), torch.cat(ats), torch.cat(bs))]
 
+    from dgmc.models.dgmc import BatchLayout
+    from dgmc.utils import GraphedTrainStep
     sizes = torch.randint(10, 21, (B, ), generator=g).tolist()
     x_s, e_s, a_s, b_s = batch(sizes)
     x_t, e_t, a_t, b_t = batch(sizes)
+    # what dgmc.utils.collate_pairs attaches on the host: (number of graphs, largest graph)
+    BatchLayout.hint(b_s, B, max(sizes))
+    BatchLayout.hint(b_t, B, max(sizes))
     y = torch.stack([torch.arange(x_s.size(0)), torch.cat([torch.randperm(n, generator=g) for n in sizes])]).to(dev)
     torch.manual_seed(0)
     model = DGMC(SplineCNN(1024, 256, 2, 2, cat=False, dropout=0.5), SplineCNN(128, 128, 2, 2, cat=True),
                  num_steps=10).to(dev).train()
-    opt = torch.optim.Adam(model.parameters(), lr=1e-3)
+    opt = torch.optim.Adam(model.parameters(), lr=1e-3, capturable=True)
 
     def step():
         opt.zero_grad(set_to_none=True)
@@ -514,16 +519,19 @@ def pascal_step_bench(dev, steps, warmup):
         opt.step()
         return loss
 
-    for _ in range(warmup):
-        step()
-    torch.cuda.synchronize()
-    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    a.record()
-    for _ in range(steps):
-        loss = step()
-    b.record()
-    torch.cuda.synchronize()
-    ms = a.elapsed_time(b) / steps
+    def timed_steps(fn):
+        for _ in range(warmup):
+            fn()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(steps):
+            out = fn()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / steps, float(out)   # (a float: keeps no autograd graph alive)
+
+    ms, loss = timed_steps(step)
     if os.environ.get('DGMC_BENCH_KINETO'):
         from torch.profiler import ProfilerActivity, profile
         with profile(activities=[ProfilerActivity.CUDA]) as prof:
@@ -535,10 +543,22 @@ def pascal_step_bench(dev, steps, warmup):
         print('kernel time per step: %.3f ms' % (sum(r[2] for r in rows) / 3e3), file=sys.stderr)
         for name, cnt, t in rows[:25]:
             print('%8.1f us/step %5d x  %s' % (t / 3, cnt // 3, name[:110]), file=sys.stderr)
-    emit({'pascal_shaped': {'graph_pairs': B, 'nodes': int(x_s.size(0)), 'edges': int(e_s.size(1)),
-                            'ms_per_step': ms, 'steps_per_s': 1e3 / ms, 'pairs_per_s': B * 1e3 / ms,
-                            'loss': loss.item(), 'execution': 'eager (batch sizes vary per step in '
-                            'the reference scripts, so no graph capture)'}})
+    # the same step captured once and replayed (a fixed padded layout: batches are bucketed by shape)
+    graphed = GraphedTrainStep(model, opt, x_s, e_s, a_s, b_s, x_t, e_t, a_t, b_t, y,
+                               loss_fn=lambda S_0, S_L, yy: model.loss(S_0, yy) + model.loss(S_L, yy),
+                               structure_is_static=True)
+    ms_graph, loss_g = timed_steps(lambda: graphed(x_s, e_s, a_s, b_s, x_t, e_t, a_t, b_t, y))
+    result = ({'pascal_shaped': {'graph_pairs': B, 'nodes': int(x_s.size(0)), 'edges': int(e_s.size(1)),
+                            'ms_per_step': ms_graph, 'steps_per_s': 1e3 / ms_graph, 'pairs_per_s': B * 1e3 / ms_graph,
+                            'eager_ms_per_step': ms, 'eager_pairs_per_s': B * 1e3 / ms,
+                            'loss': loss_g, 'eager_loss': loss,
+                            'execution': 'whole step replayed as one CUDA graph at a fixed padded layout (batches '
+                                         'bucketed by shape); eager_*: the same step issued from Python, which the '
+                                         'reference scripts do with a new batch shape every step'}})
+    del graphed, model, opt
+    sys.modules['dgmc.ops'].clear_caches()
+    torch.cuda.empty_cache()
+    return result['pascal_shaped']
 
 
 def scale_workload(n):
@@ -697,6 +717,7 @@ def main():
     ap.add_argument('--hot-kernels', action='store_true',
                     help='launch every hot kernel once inside the NVTX range "hot" and exit (for ncu --set full '
                          '--nvtx --nvtx-include "hot/"); with --scale-kernels N on the N x N pair')
+    ap.add_argument('--no-pascal', action='store_true', help='skip the PascalVOC-shaped block of the N=1 line')
     ap.add_argument('--no-scale-study', action='store_true', help='skip the large-pair step of the bench line')
     ap.add_argument('--scale-study-nodes', type=int, default=1000000, metavar='N')
     ap.add_argument('--no-roofline-1m', action='store_true', help='skip the 1M x 1M kernel sweep of the N=1 line')
@@ -754,7 +775,7 @@ def main():
         scale_kernels(args.scale_kernels, dev)
         return 0
     if args.pascal:
-        pascal_step_bench(dev, args.steps, args.warmup)
+        emit({'pascal_shaped': pascal_step_bench(dev, args.steps, args.warmup)})
         return 0
     if world > 1:
         os.environ.setdefault('TORCH_NCCL_ASYNC_ERROR_HANDLING', '0')  # collectives get graph-captured
@@ -951,6 +972,9 @@ def main():
             out['parity'] = parity
         if study is not None:
             out['scale_study'] = study
+        if world == 1 and not args.nodes and not args.k and not args.no_pascal:
+            # BASELINE.json configs[1] (dense variant, SplineCNN, 512 pairs of 10-20-node graphs): for the record
+            out['pascal_shaped'] = pascal_step_bench(dev, 10, 3)
         if world == 1 and not args.nodes and not args.k and not args.no_roofline_1m:
             # BASELINE.json configs[4] shape, kernels alone: where HBM, not latency, is the roofline
             del model

@@ -27,36 +27,77 @@ from .. import ops
 EPS = 1e-8
 
 
+class BatchLayout(object):
+    """Where the nodes of a batch of graphs sit in the padded [B, N_max] layout (PyG to_dense_batch as
+    called at dgmc.py:154-155): `slot` [sum N] = flat padded position of every real node, `mask`
+    [B, N_max].  Everything downstream un-pads / re-pads with `slot` (index_select / index_copy: no
+    boolean indexing, hence no nonzero and no host synchronisation per consensus step).
+
+    Only two numbers need the host: the number of graphs and the largest graph.  They are taken, in
+    this order, from a hint attached to the batch vector by the collation — `BatchLayout.hint(batch,
+    num_graphs, max_nodes)`, which dgmc.utils.collate_pairs does on the host, where the sizes are known
+    before the data is copied to the device — from the cache (same batch tensor as last time), or from
+    the device (two synchronisations, as in the reference)."""
+    _cache = {}
+
+    def __init__(self, batch, num_graphs, n_max):
+        self.B, self.n_max = num_graphs, n_max
+        ones = torch.ones_like(batch)
+        sizes = torch.zeros(num_graphs, dtype=batch.dtype, device=batch.device).scatter_add_(0, batch, ones)
+        first = torch.cumsum(sizes, 0) - sizes
+        self.slot = batch * n_max + (torch.arange(batch.numel(), device=batch.device) - first[batch])
+        mask = torch.zeros(num_graphs * n_max, dtype=torch.bool, device=batch.device)
+        mask[self.slot] = True
+        self.mask = mask.view(num_graphs, n_max)
+
+    @staticmethod
+    def hint(batch, num_graphs, max_nodes):
+        batch.__dgmc_layout__ = (int(num_graphs), int(max_nodes))
+        return batch
+
+    @classmethod
+    def of(cls, batch):
+        key = (batch.data_ptr(), batch.numel(), batch._version, str(batch.device))
+        hit = cls._cache.get(key)
+        if hit is not None and hit[0] is batch:
+            return hit[1]
+        known = getattr(batch, '__dgmc_layout__', None)
+        if known is None:
+            num_graphs = int(batch[-1]) + 1                                   # host sync
+            ones = torch.ones_like(batch)
+            sizes = torch.zeros(num_graphs, dtype=batch.dtype, device=batch.device).scatter_add_(0, batch, ones)
+            known = (num_graphs, int(sizes.max()))                            # host sync
+        if len(cls._cache) > 64:
+            cls._cache.clear()
+        layout = cls(batch, *known)
+        cls._cache[key] = (batch, layout)
+        return layout
+
+
+ops._EXTRA_CACHES.append(BatchLayout._cache)
+
+
 def _pad_batch(x, batch):
-    """[sum N, C] -> ([B, N_max, C] zero-padded, bool mask [B, N_max])  (PyG to_dense_batch as
-    called at dgmc.py:154-155).  batch=None means one graph: a view, no copy."""
+    """[sum N, C] -> ([B, N_max, C] zero-padded, BatchLayout or None).  batch=None means one graph: a
+    view, no copy."""
     if batch is None:
         return x.unsqueeze(0), None
-    num_graphs = int(batch[-1]) + 1
-    sizes = torch.bincount(batch, minlength=num_graphs)
-    n_max = int(sizes.max())
-    first = torch.cumsum(sizes, 0) - sizes
-    slot = batch * n_max + (torch.arange(batch.numel(), device=x.device) - first[batch])
-    dense = x.new_zeros(num_graphs * n_max, x.size(-1))
-    dense[slot] = x
-    mask = torch.zeros(num_graphs * n_max, dtype=torch.bool, device=x.device)
-    mask[slot] = True
-    return dense.view(num_graphs, n_max, -1), mask.view(num_graphs, n_max)
+    lay = BatchLayout.of(batch)
+    dense = x.new_zeros(lay.B * lay.n_max, x.size(-1)).index_copy(0, lay.slot, x)
+    return dense.view(lay.B, lay.n_max, -1), lay
 
 
-def _rows(x, mask):
+def _rows(x, lay):
     """un-pad: [B, N, R] -> [sum N, R]  (to_sparse, dgmc.py:22-23)."""
     flat = x.reshape(-1, x.size(-1))
-    return flat if mask is None else flat[mask.view(-1)]
+    return flat if lay is None else flat.index_select(0, lay.slot)
 
 
-def _repad(x, mask):
+def _repad(x, lay):
     """[sum N, R] -> [B * N_max, R], zeros in the padding (to_dense, dgmc.py:26-29)."""
-    if mask is None:
+    if lay is None:
         return x
-    out = x.new_zeros(mask.numel(), x.size(-1))
-    out[mask.view(-1)] = x
-    return out
+    return x.new_zeros(lay.B * lay.n_max, x.size(-1)).index_copy(0, lay.slot, x)
 
 
 def _sparse_coo(coords, values, size):
@@ -115,7 +156,9 @@ class DGMC(torch.nn.Module):
         B, n_s, k = S_idx.shape
         rows, cols = y[0], y[1]
         flat = S_idx.reshape(B * n_s, k)
-        if s_mask is not None:  # flat real-node index -> padded row (batched graphs only)
+        if isinstance(s_mask, BatchLayout):   # flat real-node index -> padded row, no synchronisation
+            rows = s_mask.slot[rows]
+        elif s_mask is not None:              # the reference's signature: a boolean mask [B, N_s]
             rows = torch.nonzero(s_mask.view(-1)).view(-1)[rows]
         missing = (flat[rows] != cols.view(-1, 1)).all(dim=-1)
         out = flat.clone()
@@ -168,8 +211,10 @@ class DGMC(torch.nn.Module):
         if self.detach:
             h_s, h_t = h_s.detach(), h_t.detach()
 
-        h_s, s_mask = _pad_batch(h_s, batch_s)
-        h_t, t_mask = _pad_batch(h_t, batch_t)
+        h_s, s_lay = _pad_batch(h_s, batch_s)
+        h_t, t_lay = _pad_batch(h_t, batch_t)
+        s_mask = None if s_lay is None else s_lay.mask
+        t_mask = None if t_lay is None else t_lay.mask
         assert h_s.size(0) == h_t.size(0), 'Encountered unequal batch-sizes'
         (B, N_s, C), N_t = h_s.size(), h_t.size(1)
         R_in = self.psi_2.in_channels
@@ -181,7 +226,7 @@ class DGMC(torch.nn.Module):
 
         def consensus_nodes(r_s, r_t):
             """psi_2 on both graphs, then the hoisted first MLP layer -> (P_s, P_t) flat."""
-            r_s, r_t = _rows(r_s, s_mask), _rows(r_t, t_mask)
+            r_s, r_t = _rows(r_s, s_lay), _rows(r_t, t_lay)
             if merged is not None:
                 # psi_2 shares its weights between the two graphs: run it ONCE on their disjoint
                 # union (same arithmetic per node, half the launches, twice the GEMM height)
@@ -189,10 +234,10 @@ class DGMC(torch.nn.Module):
                 p = ops.node_linear(o, w1, key=('mlp0', id(self)))
                 # b1 after re-padding: the reference applies mlp[0] to padded source rows too (their
                 # o_s is 0, so they see relu(b1 - W1 o_t), dgmc.py:217-223)
-                return _repad(p[:r_s.size(0)], s_mask) + b1, _repad(p[r_s.size(0):], t_mask)
+                return _repad(p[:r_s.size(0)], s_lay) + b1, _repad(p[r_s.size(0):], t_lay)
             o_s = self.psi_2(r_s, edge_index_s, edge_attr_s)
             o_t = self.psi_2(r_t, edge_index_t, edge_attr_t)
-            o_s, o_t = _repad(o_s, s_mask), _repad(o_t, t_mask)
+            o_s, o_t = _repad(o_s, s_lay), _repad(o_t, t_lay)
             return (ops.node_linear(o_s, w1, b1, key=('mlp0s', id(self))),
                     ops.node_linear(o_t, w1, key=('mlp0t', id(self))))
 
@@ -210,7 +255,7 @@ class DGMC(torch.nn.Module):
             else:
                 S_hat = h_s @ h_t.transpose(-1, -2)
                 S = ops.masked_softmax(S_hat, sm, tm)
-            S_0 = _rows(S, s_mask)
+            S_0 = _rows(S, s_lay)
             for step in range(num_steps):
                 if step > 0:
                     S = ops.masked_softmax(S_hat, sm, tm)
@@ -219,7 +264,7 @@ class DGMC(torch.nn.Module):
                 p_s, p_t = consensus_nodes(r_s, r_t)
                 S_hat = ops.dense_consensus(S_hat, p_s.view(B, N_s, -1), p_t.view(B, N_t, -1), w2,
                                             b2, sm, tm)
-            S_L = _rows(ops.masked_softmax(S_hat, sm, tm), s_mask)
+            S_L = _rows(ops.masked_softmax(S_hat, sm, tm), s_lay)
             return S_0, S_L
 
         # ------ sparse variant (dgmc.py:184-244) ------
@@ -228,12 +273,12 @@ class DGMC(torch.nn.Module):
             rnd_size = (B, N_s, min(self.k, N_t - self.k))
             S_rnd_idx = torch.randint(N_t, rnd_size, dtype=torch.long, device=S_idx.device)
             S_idx = torch.cat([S_idx, S_rnd_idx], dim=-1)
-            S_idx = self.__include_gt__(S_idx, s_mask, y)
+            S_idx = self.__include_gt__(S_idx, s_mask if s_lay is None else s_lay, y)
 
         cand = ops.Candidates(S_idx, N_t)
         k = cand.k
         S_hat = ops.gather_dot(h_s.reshape(B * N_s, C), h_t.reshape(B * N_t, C), cand)
-        S_0 = _rows(ops.softmax_k(S_hat), s_mask)
+        S_0 = _rows(ops.softmax_k(S_hat), s_lay)
         for _ in range(num_steps):
             S = ops.softmax_k(S_hat)
             r_s = torch.randn((B, N_s, R_in), dtype=h_s.dtype, device=h_s.device)
@@ -249,8 +294,8 @@ class DGMC(torch.nn.Module):
                 continue
             p_s, p_t = consensus_nodes(r_s, r_t)
             S_hat = ops.diff_mlp(S_hat, p_s, p_t, w2, b2, cand)
-        S_L = _rows(ops.softmax_k(S_hat), s_mask)
-        S_idx = _rows(S_idx, s_mask)
+        S_L = _rows(ops.softmax_k(S_hat), s_lay)
+        S_idx = _rows(S_idx, s_lay)
 
         # wrap as the reference does (dgmc.py:228-244)
         n_rows = x_s.size(0)

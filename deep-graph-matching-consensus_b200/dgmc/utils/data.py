@@ -42,7 +42,11 @@ class PairData(object):
         for key in self._keys:
             value = getattr(self, key)
             if torch.is_tensor(value):
-                setattr(self, key, value.to(device))
+                moved = value.to(device)
+                hint = getattr(value, '__dgmc_layout__', None)
+                if hint is not None:     # (number of graphs, largest graph) of a batch vector: see collate_pairs
+                    moved.__dgmc_layout__ = hint
+                setattr(self, key, moved)
         return self
 
     def __repr__(self):
@@ -71,6 +75,11 @@ def collate_pairs(pairs):
         off_t += pair.x_t.size(0)
     for key, parts in cols.items():
         out[key] = torch.cat(parts, dim=-1 if 'index' in key else 0)
+    # The sizes are known HERE, on the host: attach (number of graphs, largest graph) to the batch
+    # vectors so that DGMC.forward can lay out the padded batch without asking the device for them
+    # (the reference's to_dense_batch synchronises twice per side and call).
+    out['x_s_batch'].__dgmc_layout__ = (len(pairs), max(p.x_s.size(0) for p in pairs))
+    out['x_t_batch'].__dgmc_layout__ = (len(pairs), max(p.x_t.size(0) for p in pairs))
     return PairData(**out)
 
 

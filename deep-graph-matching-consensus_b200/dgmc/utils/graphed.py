@@ -32,6 +32,11 @@ class GraphedTrainStep(object):
         self.loss_fn = loss_fn or (lambda S_0, S_L, y: model.loss(S_L, y))
         dev = next(model.parameters()).device
         self.static = [None if t is None else t.to(dev).clone() for t in example_inputs]
+        for dst, src in zip(self.static, example_inputs):
+            # (number of graphs, largest graph) of a batch vector, attached by dgmc.utils.collate_pairs: the
+            # captured step keeps that padded layout, so every batch replayed through it must fit it
+            if src is not None and hasattr(src, '__dgmc_layout__'):
+                dst.__dgmc_layout__ = src.__dgmc_layout__
         self.structure_is_static = structure_is_static
         self.graph = torch.cuda.CUDAGraph()
 

@@ -84,3 +84,40 @@ def test_include_gt_rows_keep_their_own_ground_truth():
     y = torch.tensor([[0, 2, 3], [1, 9, 6]], device=DEV)     # row 0 and row 3 already contain theirs
     out = model.__include_gt__(S_idx, None, y)
     assert out.tolist() == [[[0, 1], [2, 3], [4, 9], [6, 7]]]
+
+
+def test_batched_forward_backward_makes_no_host_synchronisation():
+    """with the sizes attached by the collation (dgmc.utils.collate_pairs) a batched
+    call — dense or sparse, forward, loss and backward — never waits for the device: no boolean
+    indexing, no .item(), no bincount (checked with torch's sync debug mode)."""
+    from dgmc.models import DGMC, SplineCNN
+    from dgmc.utils.data import PairData, collate_pairs
+    g = torch.Generator().manual_seed(1)
+
+    def graph(n):
+        return dict(x=torch.randn(n, 16, generator=g), ei=torch.randint(n, (2, 4 * n), generator=g),
+                    ea=torch.rand(4 * n, 2, generator=g))
+    pairs = []
+    for _ in range(12):
+        n = int(torch.randint(5, 12, (1, ), generator=g))
+        a, b = graph(n), graph(n + 1)
+        pairs.append(PairData(x_s=a['x'], edge_index_s=a['ei'], edge_attr_s=a['ea'], x_t=b['x'],
+                              edge_index_t=b['ei'], edge_attr_t=b['ea'], y=torch.randperm(n + 1, generator=g)[:n],
+                              num_nodes=None))
+    data = collate_pairs(pairs).to('cuda')
+    y = torch.stack([torch.arange(data.y.numel(), device='cuda'), data.y])
+    torch.manual_seed(0)
+    for k in (-1, 4):
+        model = DGMC(SplineCNN(16, 32, 2, 2, cat=False, dropout=0.5), SplineCNN(8, 8, 2, 2), num_steps=3, k=k).cuda().train()
+        args = (data.x_s, data.edge_index_s, data.edge_attr_s, data.x_s_batch, data.x_t, data.edge_index_t,
+                data.edge_attr_t, data.x_t_batch)
+        model(*args, y)[1]           # warm-up: lazy one-time set-up (kernel attributes, cuBLAS handles)
+        torch.cuda.synchronize()
+        torch.cuda.set_sync_debug_mode('error')
+        try:
+            S_0, S_L = model(*args, y)
+            loss = model.loss(S_0, y) + model.loss(S_L, y)
+            loss.backward()
+        finally:
+            torch.cuda.set_sync_debug_mode('default')
+        assert torch.isfinite(loss).item()
