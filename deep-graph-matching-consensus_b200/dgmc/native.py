@@ -99,10 +99,11 @@ class RowStrided(object):
 def _ptr(t):
     if t is None:
         return None
-    if isinstance(t, RowStrided):
-        if not t.t.is_cuda:
-            raise DgmcNativeError('dgmc (B200): tensor on %s; there is no CPU fallback' % t.t.device)
-        return t.t.data_ptr()
+    if t.__class__ is RowStrided:
+        t = t.t
+        if not t.is_cuda:
+            raise DgmcNativeError('dgmc (B200): tensor on %s; there is no CPU fallback' % t.device)
+        return t.data_ptr()
     if not t.is_cuda:
         raise DgmcNativeError('dgmc (B200): tensor on %s; the kernels need CUDA tensors and there '
                               'is no CPU fallback' % t.device)
@@ -111,18 +112,22 @@ def _ptr(t):
     return t.data_ptr()
 
 
+_raw_stream = getattr(torch._C, '_cuda_getCurrentRawStream', None)
+_raw_device = getattr(torch._C, '_cuda_getDevice', None)
+
+
 def stream_ptr():
+    """The current CUDA stream of the current device as a raw cudaStream_t (fast path through torch._C:
+    this is called once per kernel launch)."""
+    if _raw_stream is not None and _raw_device is not None and torch.cuda.is_initialized():
+        return _raw_stream(_raw_device())
     if not torch.cuda.is_available():
         raise DgmcNativeError('dgmc (B200): no CUDA device; the kernels have no CPU fallback')
     return torch.cuda.current_stream().cuda_stream
 
 
 LAUNCHES = [0]  # number of native entry points called (bench.py reports it as gpu_launches)
-
-
-def _device_of(a):
-    t = a.t if isinstance(a, RowStrided) else a
-    return t.device if torch.is_tensor(t) and t.is_cuda else None
+_Tensor = torch.Tensor
 
 
 def call(name, *args):
@@ -130,16 +135,27 @@ def call(name, *args):
     kernels run on the CURRENT device and stream: tensors that live on another GPU are an error (wrap
     the call in `torch.cuda.device(tensor.device)`), not a launch on the wrong device."""
     fn = getattr(lib, name)
-    conv = [_ptr(a) if (a is None or torch.is_tensor(a) or isinstance(a, RowStrided)) else a
-            for a in args]
+    conv = []
+    first = None
     for a in args:
-        dev = _device_of(a)
-        if dev is not None:
-            if dev.index != torch.cuda.current_device():
-                raise DgmcNativeError('%s: tensor on %s but the current device is cuda:%d; use '
-                                      'torch.cuda.set_device / torch.cuda.device(...)' %
-                                      (name, dev, torch.cuda.current_device()))
-            break    # torch ops already require all tensors of a call on one device
+        if a is None:
+            conv.append(None)
+        elif isinstance(a, _Tensor):
+            if first is None:
+                first = a
+            conv.append(_ptr(a))
+        elif a.__class__ is RowStrided:
+            if first is None:
+                first = a.t
+            conv.append(_ptr(a))
+        else:
+            conv.append(a)
+    if first is not None and first.is_cuda:
+        # torch ops already require all tensors of a call on one device: check the first one
+        cur = _raw_device() if _raw_device is not None else torch.cuda.current_device()
+        if first.device.index != cur:
+            raise DgmcNativeError('%s: tensor on %s but the current device is cuda:%d; use '
+                                  'torch.cuda.set_device / torch.cuda.device(...)' % (name, first.device, cur))
     LAUNCHES[0] += 1
     rc = fn(*conv)
     if rc != 0:
