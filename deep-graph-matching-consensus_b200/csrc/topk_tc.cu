@@ -223,10 +223,10 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             tcgen05_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((buf * MH + h) * TILE_N);
             const int col0 = ct * TILE_N;
-#pragma unroll 1
-            for (int c4 = 0; c4 < TILE_N / 32; ++c4) {
+            auto scan = [&](const uint32_t (&raw)[32], int c4) {
                 float r[32];
-                tmem_ld_32x32b_x32(taddr + (uint32_t)(c4 * 32), r);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) r[i] = __uint_as_float(raw[i]);
                 const int cbase = col0 + c4 * 32;
                 const int valid = args.n_t - cbase;   // columns >= n_t are TMA zero fill: ignore them
                 unsigned hits = 0;
@@ -238,6 +238,31 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                     hits &= hits - 1;
                     const float s = select32(r, i);
                     if (s > thr) { best.insert(s, cbase + i); thr = best.threshold(); }
+                }
+            };
+            if (KP <= 16) {
+                // two register buffers: the TMEM load of the next 32 columns is in flight while this
+                // chunk is scanned (with two epilogue warps per scheduler nothing else hides its latency)
+                uint32_t ra[32], rb[32];
+                tmem_ld_32x32b_x32_issue(taddr, ra);
+                tmem_ld_wait(ra);
+                tmem_ld_32x32b_x32_issue(taddr + 32u, rb);
+                scan(ra, 0);
+                tmem_ld_wait(rb);
+                tmem_ld_32x32b_x32_issue(taddr + 64u, ra);
+                scan(rb, 1);
+                tmem_ld_wait(ra);
+                tmem_ld_32x32b_x32_issue(taddr + 96u, rb);
+                scan(ra, 2);
+                tmem_ld_wait(rb);
+                scan(rb, 3);
+            } else {
+#pragma unroll 1
+                for (int c4 = 0; c4 < TILE_N / 32; ++c4) {
+                    uint32_t ra[32];
+                    tmem_ld_32x32b_x32_issue(taddr + (uint32_t)(c4 * 32), ra);
+                    tmem_ld_wait(ra);
+                    scan(ra, c4);
                 }
             }
             tcgen05_fence_before();
