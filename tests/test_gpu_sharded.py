@@ -95,3 +95,79 @@ def test_row_sharded_matches_single_gpu():
         p.join(timeout=60)
     for rank, msg in results:
         assert msg == 'ok', 'rank %d: %s' % (rank, msg)
+
+
+def _collectives_worker(rank, world, port, out):
+    import torch.distributed as dist
+    sys.path.insert(0, os.path.join(ROOT, 'deep-graph-matching-consensus_b200'))
+    os.environ['MASTER_ADDR'], os.environ['MASTER_PORT'] = '127.0.0.1', str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device('cuda', rank)
+    dist.init_process_group('nccl', rank=rank, world_size=world, device_id=dev)
+    try:
+        from dgmc.symm import PeerCollectives
+        pc = PeerCollectives.of(None, dev, 1 << 22)
+        assert pc is not None, 'peer memory unavailable on this box'
+        g = torch.Generator(device='cpu').manual_seed(100 + rank)
+        for rows, cols in ((1, 4), (37, 8), (5000, 64)):        # all-reduce: sum, identical on all ranks
+            x = torch.randn(rows, cols, generator=g).to(dev)
+            for _ in range(3):                                   # back to back: the flag words are reused
+                pc.scratch_in(rows, cols).copy_(x)
+                got = pc.all_reduce(rows, cols).clone()
+                ref = x.clone()
+                dist.all_reduce(ref)
+                assert torch.allclose(got, ref, rtol=1e-6, atol=1e-6)
+                same = got.clone()
+                dist.broadcast(same, 0)
+                assert torch.equal(got, same), 'ranks hold different sums'
+        # all-gather / reduce-scatter with two runs per rank (source block + target block, natural order)
+        n_s, n_t, c = 1001, 777, 16
+        from dgmc.models.sharded import row_block
+        (a, b), (t0, t1) = row_block(n_s, rank, world), row_block(n_t, rank, world)
+        runs = ((a, b - a), (n_s + t0, t1 - t0))
+        max_rows = max((row_block(n_s, q, world)[1] - row_block(n_s, q, world)[0]) +
+                       (row_block(n_t, q, world)[1] - row_block(n_t, q, world)[0]) for q in range(world))
+        full = torch.randn(n_s + n_t, c, generator=torch.Generator().manual_seed(5)).to(dev)   # same on all ranks
+        mine = torch.cat([full[a:b], full[n_s + t0:n_s + t1]])
+        for _ in range(3):
+            got = pc.all_gather(mine, runs, n_s + n_t, max_rows).clone()
+            assert torch.equal(got, full)
+        contrib = torch.randn(n_s + n_t, c, generator=g).to(dev)
+        total = contrib.clone()
+        dist.all_reduce(total)
+        for _ in range(3):
+            pc.scratch_in(n_s + n_t, c).copy_(contrib)
+            got = pc.reduce_scatter(mine.size(0), c, runs, max_rows)
+            want = torch.cat([total[a:b], total[n_s + t0:n_s + t1]])
+            assert torch.allclose(got, want, rtol=1e-6, atol=1e-6)
+        # equal blocks in rank order (the default form)
+        blk = torch.randn(300, 8, generator=g).to(dev)
+        got = pc.all_gather(blk).clone()
+        ref = torch.empty(world * 300, 8, device=dev)
+        dist.all_gather_into_tensor(ref, blk)
+        assert torch.equal(got, ref)
+        assert pc.timeouts() == 0
+        out.put((rank, 'ok'))
+    except Exception:  # pragma: no cover
+        import traceback
+        out.put((rank, traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason='needs 2 GPUs')
+def test_peer_memory_collectives_match_nccl():
+    """csrc/symm.cu through dgmc.symm against torch.distributed (NCCL): sums, identical results on all
+    ranks, two-run all-gather / reduce-scatter, repeated calls (self-resetting handshakes), no timeouts."""
+    import torch.multiprocessing as mp
+    ctx = mp.get_context('spawn')
+    out = ctx.Queue()
+    port = 29700 + os.getpid() % 2000
+    procs = [ctx.Process(target=_collectives_worker, args=(r, 2, port, out)) for r in range(2)]
+    for p in procs:
+        p.start()
+    results = [out.get(timeout=300) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, msg in results:
+        assert msg == 'ok', 'rank %d: %s' % (rank, msg)
