@@ -795,6 +795,8 @@ def main():
         torch.cuda.synchronize()
 
     if args.profile_eager:
+        # backward on the calling thread: NVTX ranges (which ncu filters on) are per thread
+        torch.autograd.set_multithreading_enabled(False)
         for _ in range(args.warmup):
             train_step(model, opt, d)
         torch.cuda.synchronize()
