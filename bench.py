@@ -742,7 +742,10 @@ def main():
               'loss + bwd + Adam' % (w['name'], w['n_s'], w['n_t'], w['feat'], w['feat'], w['dim'],
                                      w['layers'], w['rnd_dim'], w['rnd_dim'], w['layers'], w['k'],
                                      w['k'], w['num_steps'], w['train_pairs']),
-              'baseline_config': 'BASELINE.json configs[2]'}
+              'baseline_config': 'BASELINE.json configs[2]',
+              # (the same dictionary in both arms; how each arm executes the workload is in `execution`)
+              'l2': 'working set per step (inputs + saved activations, ~1 GB) exceeds the 126 MB L2; '
+                    'per-kernel roofline timings flush L2 with a 256 MB write'}
 
     if args.impl == 'reference':
         if rank != 0:
@@ -756,6 +759,7 @@ def main():
             'steps': n, 'warmup': wu, 'ms_per_step': dt * 1e3, 'higher_is_better': True,
             'scaling': 'strong', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
             'config': config,
+            'execution': {'parallelism': '%d host threads' % cores, 'step': what},
             'cpu_baseline': {'value': sps, 'unit': 'steps/s', 'cores': cores, 'kind': kind,
                              'sample': sample},
             'e2e': {'value': sps, 'unit': 'steps/s', 'h2d_bytes_per_step': 0,
@@ -952,17 +956,16 @@ def main():
             # one job = one graph pair whatever N is: its source rows are divided over the GPUs
             'scaling': 'strong', 'vs_baseline': None, 'dtype': 'f32',
             'data': 'synthetic',
-            'config': dict(config, parallelism=('source rows of S sharded over %d GPUs; psi_1 node-sharded; psi_2 %s; '
+            'config': config,
+            'execution': dict(parallelism=('source rows of S sharded over %d GPUs; psi_1 node-sharded; psi_2 %s; '
                                                 'collectives: the library\'s peer-memory kernels over NVLink '
                                                 '(r_t all-reduce per consensus step, layer all-gathers)' %
                                                 (world, 'node-sharded' if (w['n_s'] + w['n_t'] >= 150000 or
                                                                           os.environ.get('DGMC_SHARD_PSI') == '1')
                                                  else 'replicated')) if world > 1 else 'single GPU',
-                           execution='whole step (zero_grad+fwd+loss+bwd+Adam) replayed as one CUDA '
-                                     'graph (dgmc.utils.GraphedTrainStep); eager_ms_per_step is the '
-                                     'same step issued from Python',
-                           l2='working set per step (inputs + saved activations, ~1 GB) exceeds the '
-                              '126 MB L2; per-kernel roofline timings flush L2 with a 256 MB write'),
+                              step='whole step (zero_grad+fwd+loss+bwd+Adam) replayed as one CUDA '
+                                   'graph (dgmc.utils.GraphedTrainStep); eager_ms_per_step is the '
+                                   'same step issued from Python'),
             'clocks': clocks.summary(),
             'e2e': {'value': e2e_value, 'unit': 'steps/s', 'h2d_bytes_per_step': h2d,
                     'd2h_bytes_per_step': 4},

@@ -151,6 +151,28 @@ def _tile_order(ptr, n, tile=32):
 
 
 class _RelOperator(object):
+    # row orders for the fused RelConv kernel: computed on first use (the default route never asks)
+    @property
+    def f_order(self):
+        if getattr(self, '_f_order', None) is None:
+            self._f_order = _tile_order(self.f_ptr, self.n_out)
+        return self._f_order
+
+    @property
+    def t_order(self):
+        if getattr(self, '_t_order', None) is None:
+            self._t_order = _tile_order(self.t_ptr, self.n_out)
+        return self._t_order
+
+    def _t(self):
+        if getattr(self, '_t_built', None) is None:
+            self._t_built = self._t_make()
+        return self._t_built
+
+    t_ptr = property(lambda self: self._t()[0])
+    t_src = property(lambda self: self._t()[1])
+    t_w = property(lambda self: self._t()[2])
+
     @classmethod
     def concat(cls, a, b):
         """Operator of the disjoint union of two graphs (b's nodes numbered after a's) from the two
@@ -169,10 +191,9 @@ class _RelOperator(object):
         # its transpose [N, 3N]: segments = node ids, sources = rows of the forward operator
         self.b_ptr, self.b_src, self.b_w, self.b_seg = join(a.b_ptr, b.b_ptr, a.b_src, b.b_src, a.b_w, b.b_w,
                                                             a.b_seg, b.b_seg, 3 * n_a, n_a)
-        # operator of the input gradient, again [3N, N] (see __init__)
-        self.t_ptr, self.t_src, self.t_w, _ = join(a.t_ptr, b.t_ptr, a.t_src, b.t_src, a.t_w, b.t_w,
-                                                   a.t_ptr[:0], b.t_ptr[:0], n_a, 0)
-        self.f_order, self.t_order = _tile_order(self.f_ptr, self.n_out), _tile_order(self.t_ptr, self.n_out)
+        # operator of the input gradient, again [3N, N] (see __init__): joined on first use
+        self._t_make = lambda: join(a.t_ptr, b.t_ptr, a.t_src, b.t_src, a.t_w, b.t_w,
+                                    a.t_ptr[:0], b.t_ptr[:0], n_a, 0)[:3]
         return self
 
     def __init__(self, graph):
@@ -200,11 +221,13 @@ class _RelOperator(object):
         # (P g)[j] = sum_{j -> i} g[i] / deg_in(i)  and  (Q g)[j] = sum_{i -> j} g[i] / deg_out(i):
         # row 3j+1 lists the out-neighbours of j weighted by THEIR in-degree, row 3j+2 its in-neighbours
         # weighted by their out-degree.
-        t_rows = torch.cat([3 * node, 3 * src + 1, 3 * dst + 2])
-        t_cols = torch.cat([node, dst, src])
-        self.t_ptr, perm = csr_build(t_rows, 3 * n)
-        self.t_src, self.t_w = t_cols[perm.long()].contiguous(), w[perm.long()].contiguous()
-        self.f_order, self.t_order = _tile_order(self.f_ptr, n), _tile_order(self.t_ptr, n)
+        # (built on first use: only the fused RelConv kernel reads it)
+        def make():
+            t_rows = torch.cat([3 * node, 3 * src + 1, 3 * dst + 2])
+            t_cols = torch.cat([node, dst, src])
+            t_ptr, t_perm = csr_build(t_rows, 3 * n)
+            return t_ptr, t_cols[t_perm.long()].contiguous(), w[t_perm.long()].contiguous()
+        self._t_make = make
 
 
 class MergedPair(object):
