@@ -3,11 +3,12 @@
 `PeerCollectives` owns one symmetric allocation per process group (torch.distributed._symmetric_memory
 does the allocation and the exchange of the peer mappings — plumbing) and runs the library's own
 kernels on it (csrc/symm.cu: dgmc_sym_all_reduce / all_gather / reduce_scatter): every rank reads and
-writes its peers' buffers directly (2 GPUs: 22 us per 5 MB all-reduce where NCCL takes 43 us, 8-10 us per
+writes its peers' buffers directly (2 GPUs: 22 us per 5 MB all-reduce where NCCL takes 43 us, 14-17 us per
 all-gather / reduce-scatter of 1 MB blocks against 19-21 us), and every
 rank receives bit-identical sums.  Layout of the allocation: [flag words | input scratch | output
-scratch]; results are copied out (or consumed) before the next call reuses the scratch — the next call's
-first handshake is what makes that safe across ranks.
+scratch]; results are copied out (or consumed) before the next call reuses the scratch — every call opens
+and closes with a handshake, which is what makes that safe across ranks (also across replays of a
+captured graph).
 
 Used when the group's ranks are CUDA devices of one node with peer access; otherwise (CPU / gloo tests,
 no NVLink) `PeerCollectives.of()` returns None and the callers use torch.distributed collectives.
@@ -33,16 +34,14 @@ class PeerCollectives(object):
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
         self.pad_bytes = (int(query('dgmc_sym_pad_bytes')) + 255) // 256 * 256
         self.scratch_bytes = (int(scratch_bytes) + 255) // 256 * 256
-        # [flag words | input scratch A, B | output scratch A, B]: all_gather alternates between the two
-        # output regions and reduce_scatter between the two input regions, which saves one handshake each
-        total = self.pad_bytes + 4 * self.scratch_bytes
-        self.flip_in = self.flip_out = 0
+        # [flag words | input scratch | output scratch]
+        total = self.pad_bytes + 2 * self.scratch_bytes
         self.buf = symm_mem.empty(total, dtype=torch.uint8, device=device)
         self.buf.zero_()
         self.handle = symm_mem.rendezvous(self.buf, group=dist.group.WORLD if group is None else group)
         assert self.handle.world_size == self.world and self.handle.rank == self.rank
         self.bases = (ctypes.c_void_p * self.world)(*[int(p) for p in self.handle.buffer_ptrs])
-        self.in_off, self.out_off = self.pad_bytes, self.pad_bytes + 2 * self.scratch_bytes
+        self.in_off, self.out_off = self.pad_bytes, self.pad_bytes + self.scratch_bytes
         # NVLink-SHARP multicast mapping of the allocation (0 when the fabric has none).  Opt-in: on two
         # GPUs the switch reduction measured SLOWER than peer loads (26.8 vs 22.5 us per 5 MB all-reduce)
         mc = int(getattr(self.handle, 'multicast_ptr', 0) or 0)
@@ -58,10 +57,10 @@ class PeerCollectives(object):
 
     def scratch_in(self, rows, cols):
         """Where the NEXT all_reduce / reduce_scatter call reads this rank's contribution."""
-        return self._view(self.in_off + self.flip_in * self.scratch_bytes, rows, cols)
+        return self._view(self.in_off, rows, cols)
 
     def scratch_out(self, rows, cols):
-        return self._view(self.out_off + self.flip_out * self.scratch_bytes, rows, cols)
+        return self._view(self.out_off, rows, cols)
 
     # ---- collectives -------------------------------------------------------------------------------
     def all_reduce(self, rows, cols):
@@ -69,8 +68,8 @@ class PeerCollectives(object):
         (valid until the next collective of this object)."""
         n = rows * cols
         assert n % 4 == 0
-        call('dgmc_sym_all_reduce', self.bases, self.multicast, self.rank, self.world, self.in_off + self.flip_in * self.scratch_bytes,
-             self.out_off + self.flip_out * self.scratch_bytes, 0, n, stream_ptr())
+        call('dgmc_sym_all_reduce', self.bases, self.multicast, self.rank, self.world, self.in_off, self.out_off, 0, n,
+             stream_ptr())
         return self.scratch_out(rows, cols)
 
     def all_gather(self, x, runs=None, total_rows=None, max_rows=None):
@@ -85,10 +84,11 @@ class PeerCollectives(object):
             runs, total_rows, max_rows = ((self.rank * x.size(0), x.size(0)), (0, 0)), self.world * x.size(0), x.size(0)
         (r0, n0), (r1, n1) = runs
         assert n0 + n1 == x.size(0) and total_rows * c * 4 <= self.scratch_bytes
-        self.flip_out ^= 1     # the other region: peers may still be reading the previous result
-        call('dgmc_sym_all_gather', self.bases, self.rank, self.world, x,
-             self.out_off + self.flip_out * self.scratch_bytes, 0, r0 * c, n0 * c, r1 * c, n1 * c, max_rows * c,
-             0, stream_ptr())
+        # both handshakes, always: the C ABI lets a caller that alternates between two output regions skip
+        # the opening one, but a replayed CUDA graph repeats the region choice made at capture time, so
+        # alternation cannot be guaranteed across replays (an odd number of calls per graph breaks it)
+        call('dgmc_sym_all_gather', self.bases, self.rank, self.world, x, self.out_off, 0, r0 * c, n0 * c,
+             r1 * c, n1 * c, max_rows * c, 1, stream_ptr())
         return self.scratch_out(total_rows, c)
 
     def reduce_scatter(self, rows, cols, runs=None, max_rows=None):
@@ -100,10 +100,8 @@ class PeerCollectives(object):
         (r0, n0), (r1, n1) = runs
         assert n0 + n1 == rows
         out = torch.empty(rows, cols, dtype=torch.float32, device=self.buf.device)
-        call('dgmc_sym_reduce_scatter', self.bases, self.rank, self.world,
-             self.in_off + self.flip_in * self.scratch_bytes, out, 0, r0 * cols, n0 * cols, r1 * cols, n1 * cols,
-             max_rows * cols, 0, stream_ptr())
-        self.flip_in ^= 1      # peers may still be reading this input: the next one goes to the other region
+        call('dgmc_sym_reduce_scatter', self.bases, self.rank, self.world, self.in_off, out, 0, r0 * cols,
+             n0 * cols, r1 * cols, n1 * cols, max_rows * cols, 1, stream_ptr())     # both handshakes, see all_gather
         return out
 
     def timeouts(self):
