@@ -71,7 +71,8 @@ def test_relconv_fused_matches_fp64_and_unfused(n, c, c_out, edges, hub, relu):
     ref = run(lambda xs, ws, b: (_reference(xs, ei, ws[0], ws[1], ws[2], b, relu), xs), torch.float64, 'cpu')
 
     graph = ops.GraphCSR(ei.cuda(), n)
-    graph.rel   # build the operator now: its sorts are not part of the layer
+    rel = graph.rel   # build the operator (and what only the fused kernel reads) now: not part of the layer
+    rel.t_ptr, rel.f_order, rel.t_order
 
     def fused(xs, ws, b):
         assert ops.relconv_fused_ok(xs, graph.rel, c_out)
