@@ -279,19 +279,26 @@ class DGMC(torch.nn.Module):
         k = cand.k
         S_hat = ops.gather_dot(h_s.reshape(B * N_s, C), h_t.reshape(B * N_t, C), cand)
         S_0 = _rows(ops.softmax_k(S_hat), s_lay)
+        one_pair = merged is not None and s_mask is None and t_mask is None
         for _ in range(num_steps):
             S = ops.softmax_k(S_hat)
-            r_s = torch.randn((B, N_s, R_in), dtype=h_s.dtype, device=h_s.device)
-            r_t = ops.transport(S, r_s.view(B * N_s, R_in), cand)
-            if merged is not None and s_mask is None and t_mask is None:
-                # one un-padded pair: psi_2 and the hoisted first MLP layer on the merged node table,
-                # which K6 reads (and whose gradient its backward writes) as one tensor
-                # b1 belongs to the source rows: added by the GEMM epilogue, its gradient summed by
-                # the weight-gradient kernel (no separate add / column-sum kernels)
-                x0 = torch.cat([r_s.view(B * N_s, R_in), r_t], dim=0)
-                p = self._psi_2_then_lin1(x0, merged, w1, b1, B * N_s)
+            if one_pair:
+                # one un-padded pair: psi_2 and the hoisted first MLP layer on the merged node table
+                # [source rows ; target rows], which K6 reads (and whose gradient its backward writes) as
+                # one tensor.  The indicators are drawn, and the transport is written, straight into
+                # that table (no concatenation).  b1 belongs to the source rows: added by the GEMM
+                # epilogue, its gradient summed by the weight-gradient kernel.
+                x0 = torch.empty(B * N_s + cand.targets, R_in, dtype=h_s.dtype, device=h_s.device)
+                top = x0[:B * N_s]
+                r_s = torch.randn((B, N_s, R_in), dtype=h_s.dtype, device=h_s.device, out=top.view(B, N_s, R_in))
+                if r_s.data_ptr() != top.data_ptr():      # a replayed draw (tests): copy it in
+                    top.copy_(r_s.reshape(B * N_s, R_in))
+                r_t = ops.transport(S, top, cand, out=x0[B * N_s:])
+                p = self._psi_2_then_lin1(ops.join_rows(x0, top, r_t), merged, w1, b1, B * N_s)
                 S_hat = ops.diff_mlp_merged(S_hat, p, B * N_s, None, w2, b2, cand)
                 continue
+            r_s = torch.randn((B, N_s, R_in), dtype=h_s.dtype, device=h_s.device)
+            r_t = ops.transport(S, r_s.view(B * N_s, R_in), cand)
             p_s, p_t = consensus_nodes(r_s, r_t)
             S_hat = ops.diff_mlp(S_hat, p_s, p_t, w2, b2, cand)
         S_L = _rows(ops.softmax_k(S_hat), s_lay)

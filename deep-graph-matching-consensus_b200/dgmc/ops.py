@@ -1018,6 +1018,26 @@ def join_slices(buf, own_grad, *parts):
     return _JoinSlices.apply(buf, own_grad, *parts)
 
 
+class _JoinRows(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, buf, top, bottom):
+        n = top.size(0)
+        assert top.data_ptr() == buf.data_ptr() and bottom.data_ptr() == buf[n:].data_ptr() \
+            and n + bottom.size(0) == buf.size(0)
+        ctx.n = n
+        return buf.view_as(buf)
+
+    @staticmethod
+    def backward(ctx, g):
+        return None, g[:ctx.n], g[ctx.n:]
+
+
+def join_rows(buf, top, bottom):
+    """torch.cat([top, bottom], dim=0) when both were written straight into `buf` (top = buf[:n],
+    bottom = buf[n:]): no copy in the forward pass, row views of the gradient in the backward pass."""
+    return _JoinRows.apply(buf, top, bottom)
+
+
 def rel_aggregate(x, graph):
     """-> [N, 3C] = [x | mean_{j->i} x_j | mean_{i->j} x_j]  (the two propagate calls of
     rel.py:27-30, taken BEFORE the linear maps: mean(lin(x_j)) == lin(mean(x_j)))."""
