@@ -83,9 +83,13 @@ struct DenseArgs {
     int B, n_s, n_t, g;                             // g = graphs per tile
 };
 
-// LT_ACC: accumulator pairs [H | L] the k8 steps alternate between (2 for long reductions, see the
-// MMA issuer; 1 for k_in <= 128, which leaves room for a second accumulator set at BN = 128)
-template <int BN, int LT_ACC, bool DENSE>
+// Accumulator layout of one set (see the MMA issuer):
+//   SHARED_L = false: LT_ACC pairs [H | L] the k8 steps alternate between (1 for k_in <= 128, which
+//                     leaves room for a second set at BN = 128; 2 up to k_in = 384)
+//   SHARED_L = true:  LT_ACC accumulators H_0 .. H_{LT_ACC-1} and ONE L behind them — for the long
+//                     reductions of psi_1 (k_in = 768 ... 1068), with BN = 64 and LT_ACC = 7 so that no
+//                     accumulator receives more than ~20 adds
+template <int BN, int LT_ACC, bool DENSE, bool SHARED_L = false>
 __global__ void __launch_bounds__(LT_THREADS, 1)
 linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_whi,
                  const __grid_constant__ CUtensorMap map_wlo, const __grid_constant__ CUtensorMap map_y,
@@ -95,7 +99,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     constexpr int B_BYTES = BN * LT_KB * 4;
     constexpr int STAGE_BYTES = 2 * LT_A_BYTES + 2 * B_BYTES;
     constexpr int NSTAGE = lt_stages(BN);
-    constexpr int ACC_COLS = 2 * LT_ACC * BN;          // one accumulator set: LT_ACC pairs [H | L]
+    constexpr int ACC_COLS = SHARED_L ? (LT_ACC + 1) * BN : 2 * LT_ACC * BN;
     // accumulator sets: with two, the epilogue of one tile overlaps the MMAs of the next
     constexpr int NBUF = LT_TMEM_COLS / ACC_COLS >= 2 ? 2 : 1;
     extern __shared__ uint8_t smem_raw[];
@@ -162,7 +166,10 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
             // The tensor core TRUNCATES when it adds an instruction's result to the accumulator, so
             // the error grows with the number of instructions per accumulator: the small lo terms
             // get their own accumulator L, and successive k8 steps alternate between LT_ACC column
-            // pairs, which the epilogue adds in round-to-nearest fp32.
+            // pairs, which the epilogue adds in round-to-nearest fp32.  SHARED_L: three N = BN MMAs per
+            // k8 step instead — X_hi x W_hi -> H_j (j rotates over LT_ACC accumulators), X_hi x W_lo -> L,
+            // X_lo x W_hi -> L: the lo terms are 2^-11 smaller, so one accumulator takes all of them (its
+            // truncation error is 2^-11 of what it would be in H) and TMEM holds more H accumulators.
             constexpr uint32_t idesc_wide = (1u << 4) | (2u << 7) | (2u << 10) |
                                             ((uint32_t)((2 * BN) >> 3) << 17) | ((uint32_t)(LT_BM >> 4) << 24);
             constexpr uint32_t idesc_lo = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) |
@@ -181,12 +188,20 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                     const uint32_t st = smem_u32(smem + (size_t)s * STAGE_BYTES);
                     const uint64_t d_ahi = umma_desc_sw128(st), d_alo = umma_desc_sw128(st + LT_A_BYTES);
                     const uint64_t d_b = umma_desc_sw128(st + 2 * LT_A_BYTES);   // W_hi rows, then W_lo rows
+                    const uint64_t d_blo = umma_desc_sw128(st + 2 * LT_A_BYTES + B_BYTES);
 #pragma unroll
                     for (int ks = 0; ks < LT_KB / 8; ++ks, ++step) {   // +32 bytes per K=8 step inside the swizzled row
                         const uint64_t o = (uint64_t)(2 * ks);
-                        const uint32_t d = acc + (uint32_t)((step % LT_ACC) * 2 * BN);
-                        tcgen05_mma_tf32(d, d_ahi + o, d_b + o, idesc_wide, (uint32_t)(step >= LT_ACC));
-                        tcgen05_mma_tf32(d + BN, d_alo + o, d_b + o, idesc_lo, 1u);
+                        if (SHARED_L) {
+                            const uint32_t d_h = acc + (uint32_t)((step % LT_ACC) * BN), d_l = acc + (uint32_t)(LT_ACC * BN);
+                            tcgen05_mma_tf32(d_h, d_ahi + o, d_b + o, idesc_lo, (uint32_t)(step >= LT_ACC));
+                            tcgen05_mma_tf32(d_l, d_ahi + o, d_blo + o, idesc_lo, (uint32_t)(step > 0));
+                            tcgen05_mma_tf32(d_l, d_alo + o, d_b + o, idesc_lo, 1u);
+                        } else {
+                            const uint32_t d = acc + (uint32_t)((step % LT_ACC) * 2 * BN);
+                            tcgen05_mma_tf32(d, d_ahi + o, d_b + o, idesc_wide, (uint32_t)(step >= LT_ACC));
+                            tcgen05_mma_tf32(d + BN, d_alo + o, d_b + o, idesc_lo, 1u);
+                        }
                     }
                     tcgen05_commit(&empty[s]);
                     if (++s == NSTAGE) { s = 0; phase ^= 1u; }
@@ -303,7 +318,23 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
             for (int cb = 0; cb < BN; cb += 32) {
                 if (n0 + cb >= n_out) break;               // warp-uniform; cb = 0 is always live
                 float r[32];
-                {
+                if (SHARED_L) {
+                    // H_0 + H_1 + ... + L, two TMEM loads per wait (LT_ACC + 1 is even), the small L last
+                    static_assert(!SHARED_L || (LT_ACC + 1) % 2 == 0, "accumulators are read in pairs");
+                    const uint32_t lane_base = tmem_d + ((uint32_t)(quarter * 32) << 16) +
+                                               (uint32_t)(buf * ACC_COLS + cb);
+                    float q[32];
+                    tmem_ld_32x32b_x32_pair(lane_base, lane_base + (uint32_t)BN, r, q);
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) r[j] += q[j];
+#pragma unroll
+                    for (int a = 2; a < LT_ACC + 1; a += 2) {
+                        float p2[32];
+                        tmem_ld_32x32b_x32_pair(lane_base + (uint32_t)(a * BN), lane_base + (uint32_t)((a + 1) * BN), p2, q);
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) r[j] = (r[j] + p2[j]) + q[j];
+                    }
+                } else {
                     const uint32_t lane_base = tmem_d + ((uint32_t)(quarter * 32) << 16) +
                                                (uint32_t)(buf * ACC_COLS + cb);
                     float l[32];
@@ -407,7 +438,7 @@ static int lt_make_map(CUtensorMap* map, const void* base, long long rows, long 
 static int lt_bn(int n_out) { return n_out <= 64 ? 64 : 128; }
 static int lt_round(int v, int m) { return (v + m - 1) / m * m; }
 
-template <int BN, int ACC>
+template <int BN, int ACC, bool SHARED_L = false>
 static int lt_launch(const CUtensorMap& mx, const CUtensorMap& mh, const CUtensorMap& ml,
                      const CUtensorMap& my, int y_tma, const float* bias, long long bias_rows, int relu, float* y, long long ldy, long long rows, int n_out, int k_blocks, int n_pad,
                      cudaStream_t stream) {
@@ -417,7 +448,7 @@ static int lt_launch(const CUtensorMap& mx, const CUtensorMap& mh, const CUtenso
     const size_t smem = (size_t)lt_stages(BN) * STAGE + 4 * LT_OUT_BYTES + (3 * LT_MAX_STAGES + 6) * 8 + 1024;
     static DeviceOnce configured;
     if (!configured.done()) {
-        if (cudaFuncSetAttribute(linear_tc_kernel<BN, ACC, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        if (cudaFuncSetAttribute(linear_tc_kernel<BN, ACC, false, SHARED_L>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)smem) != cudaSuccess) {
             set_error("linear_tc: cannot set %zu bytes of dynamic shared memory", smem);
             return DGMC_ERR_CUDA;
@@ -428,7 +459,7 @@ static int lt_launch(const CUtensorMap& mx, const CUtensorMap& mh, const CUtenso
     const long long tiles = (long long)n_tiles_n * ((rows + LT_BM - 1) / LT_BM);
     if (tiles > 0x7fffffffLL) { set_error("linear_tc: too many tiles"); return DGMC_ERR_UNSUPPORTED; }
     const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
-    linear_tc_kernel<BN, ACC, false><<<grid, LT_THREADS, smem, stream>>>(mx, mh, ml, my, y_tma, bias, bias_rows, relu, y,
+    linear_tc_kernel<BN, ACC, false, SHARED_L><<<grid, LT_THREADS, smem, stream>>>(mx, mh, ml, my, y_tma, bias, bias_rows, relu, y,
                                                                    ldy, rows, n_out, k_blocks, n_tiles_n, (int)tiles,
                                                                    no_dense);
     return DGMC_OK;
@@ -479,8 +510,14 @@ static int linear_tc_impl(const float* x, int64_t ldx, const void* split_weight,
                   "aligned base and pitch)", (long long)rows, n_out, k_in, (long long)ldx);
         return DGMC_ERR_UNSUPPORTED;
     }
-    const int bn = tc::lt_bn(n_out);
-    const int n_pad = tc::lt_round(n_out, bn), k_pad = tc::lt_round(k_in, tc::LT_KB);
+    // the split weight is padded to lt_bn(n_out) rows (workspace layout); long reductions (more than 12
+    // k blocks: psi_1's 768 ... 1068 columns) run on 64-column tiles whatever n_out is, so that seven H
+    // accumulators fit into TMEM — every accumulator then sees <= ~20 truncating adds.  Measured on psi_1
+    // at the DBP15K shape against fp64: 7.4e-7 of max|h| (IEEE fp32 on the CPU: 8.4e-7; two pairs on
+    // 128-column tiles: 2.4e-6), at 1.8x the time of those GEMMs (+0.33 ms per DBP15K training step).
+    const int n_pad = tc::lt_round(n_out, tc::lt_bn(n_out)), k_pad = tc::lt_round(k_in, tc::LT_KB);
+    const bool long_k = k_pad / tc::LT_KB > 12;
+    const int bn = long_k ? 64 : tc::lt_bn(n_out);
     const float* hi = static_cast<const float*>(split_weight);
     const float* lo = hi + (size_t)n_pad * k_pad;
     CUtensorMap mx, mh, ml;
@@ -496,7 +533,8 @@ static int linear_tc_impl(const float* x, int64_t ldx, const void* split_weight,
     int e;
     const bool short_k = k_blocks <= 4;
 #define DGMC_LT_ARGS mx, mh, ml, my, y_tma, bias, bias_rows, relu, y, ldy, rows, n_out, k_blocks, n_pad, stream
-    if (bn == 64) e = short_k ? tc::lt_launch<64, 1>(DGMC_LT_ARGS) : tc::lt_launch<64, 2>(DGMC_LT_ARGS);
+    if (long_k) e = tc::lt_launch<64, 7, true>(DGMC_LT_ARGS);
+    else if (bn == 64) e = short_k ? tc::lt_launch<64, 1>(DGMC_LT_ARGS) : tc::lt_launch<64, 2>(DGMC_LT_ARGS);
     else          e = short_k ? tc::lt_launch<128, 1>(DGMC_LT_ARGS) : tc::lt_launch<128, 2>(DGMC_LT_ARGS);
 #undef DGMC_LT_ARGS
     if (e) return e;
