@@ -84,22 +84,24 @@ struct DenseArgs {
 };
 
 // Accumulator layout of one set (see the MMA issuer):
-//   SHARED_L = false: LT_ACC pairs [H | L] the k8 steps alternate between (1 for k_in <= 128, which
-//                     leaves room for a second set at BN = 128; 2 up to k_in = 384)
-//   SHARED_L = true:  LT_ACC accumulators H_0 .. H_{LT_ACC-1} and ONE L behind them — for the long
-//                     reductions of psi_1 (k_in = 768 ... 1068), with BN = 64 and LT_ACC = 7 so that no
-//                     accumulator receives more than ~20 adds
-template <int BN, int LT_ACC, bool DENSE, bool SHARED_L = false>
+//   LT_ACC pairs [H | L] the k8 steps alternate between (1 for k_in <= 128, which leaves room for a
+//   second set at BN = 128; 2 up to k_in = 384).
+//   RANGE > 0 (long reductions: psi_1, k_in = 768 ... 1068): the reduction is cut into ranges of RANGE
+//   k blocks; each range fills one accumulator set [H | L] (LT_ACC = 1: two sets in TMEM) and the
+//   epilogue warps drain it into REGISTER running sums (round-to-nearest fp32) while the next range's
+//   MMAs fill the other set — 4 RANGE truncating adds per accumulator whatever k_in is, on full
+//   128-column tiles.
+template <int BN, int LT_ACC, bool DENSE, int RANGE = 0>
 __global__ void __launch_bounds__(LT_THREADS, 1)
 linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_whi,
                  const __grid_constant__ CUtensorMap map_wlo, const __grid_constant__ CUtensorMap map_y,
                  int y_tma, const float* __restrict__ bias, long long bias_rows, int relu, float* __restrict__ y,
                  long long ldy,
-                 long long rows, int n_out, int k_blocks, int n_tiles_n, int n_tiles, const DenseArgs dense) {
+                 long long rows, int n_out, int k_blocks, int n_tiles_n, int n_tiles, int bm, const DenseArgs dense) {
     constexpr int B_BYTES = BN * LT_KB * 4;
     constexpr int STAGE_BYTES = 2 * LT_A_BYTES + 2 * B_BYTES;
     constexpr int NSTAGE = lt_stages(BN);
-    constexpr int ACC_COLS = SHARED_L ? (LT_ACC + 1) * BN : 2 * LT_ACC * BN;
+    constexpr int ACC_COLS = 2 * LT_ACC * BN;          // one accumulator set: LT_ACC pairs [H | L]
     // accumulator sets: with two, the epilogue of one tile overlaps the MMAs of the next
     constexpr int NBUF = LT_TMEM_COLS / ACC_COLS >= 2 ? 2 : 1;
     extern __shared__ uint8_t smem_raw[];
@@ -143,12 +145,12 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
             // ================= TMA producer =================
             int s = 0; uint32_t phase = 0;
             for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-                const int m0 = DENSE ? tile * dense.g * dense.n_s : (tile / n_tiles_n) * LT_BM;
+                const int m0 = DENSE ? tile * dense.g * dense.n_s : (tile / n_tiles_n) * bm;
                 const int n0 = DENSE ? tile * dense.g * dense.n_t : (tile % n_tiles_n) * BN;
                 for (int kb = 0; kb < k_blocks; ++kb) {
                     mbar_wait(&empty[s], phase ^ 1u);
                     uint8_t* st = smem + (size_t)s * STAGE_BYTES;
-                    mbar_expect_tx(&full[s], (uint32_t)(LT_A_BYTES + 2 * B_BYTES));
+                    mbar_expect_tx(&full[s], (uint32_t)(bm * LT_KB * 4 + 2 * B_BYTES));   // X box: bm rows
                     tma_load_2d(st, &map_x, &full[s], kb * LT_KB, m0);
                     tma_load_2d(st + 2 * LT_A_BYTES, &map_whi, &full[s], kb * LT_KB, n0);
                     tma_load_2d(st + 2 * LT_A_BYTES + B_BYTES, &map_wlo, &full[s], kb * LT_KB, n0);
@@ -166,42 +168,35 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
             // The tensor core TRUNCATES when it adds an instruction's result to the accumulator, so
             // the error grows with the number of instructions per accumulator: the small lo terms
             // get their own accumulator L, and successive k8 steps alternate between LT_ACC column
-            // pairs, which the epilogue adds in round-to-nearest fp32.  SHARED_L: three N = BN MMAs per
-            // k8 step instead — X_hi x W_hi -> H_j (j rotates over LT_ACC accumulators), X_hi x W_lo -> L,
-            // X_lo x W_hi -> L: the lo terms are 2^-11 smaller, so one accumulator takes all of them (its
-            // truncation error is 2^-11 of what it would be in H) and TMEM holds more H accumulators.
+            // pairs, which the epilogue adds in round-to-nearest fp32.  With RANGE > 0 an accumulator set
+            // only ever receives RANGE k blocks (4 RANGE adds): see the epilogue.
             constexpr uint32_t idesc_wide = (1u << 4) | (2u << 7) | (2u << 10) |
                                             ((uint32_t)((2 * BN) >> 3) << 17) | ((uint32_t)(LT_BM >> 4) << 24);
             constexpr uint32_t idesc_lo = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) |
                                           ((uint32_t)(LT_BM >> 4) << 24);
             int s = 0; uint32_t phase = 0; int it = 0;
-            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+            const int per = RANGE > 0 ? RANGE : k_blocks;       // k blocks per accumulator set
+            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x)
+            for (int kb0 = 0; kb0 < k_blocks; kb0 += per, ++it) {
                 const int buf = it % NBUF, use = it / NBUF;
                 mbar_wait(&acc_empty[buf], (uint32_t)((use & 1) ^ 1));   // epilogue has drained this set
                 tcgen05_fence_after();
                 const uint32_t acc = tmem_d + (uint32_t)(buf * ACC_COLS);
                 int step = 0;
-                for (int kb = 0; kb < k_blocks; ++kb) {
+                const int kb1 = kb0 + per < k_blocks ? kb0 + per : k_blocks;
+                for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&full[s], phase);          // W tiles (written by TMA)
                     mbar_wait(&split_done[s], phase);    // X tiles (rewritten by warps 2-5)
                     tcgen05_fence_after();
                     const uint32_t st = smem_u32(smem + (size_t)s * STAGE_BYTES);
                     const uint64_t d_ahi = umma_desc_sw128(st), d_alo = umma_desc_sw128(st + LT_A_BYTES);
                     const uint64_t d_b = umma_desc_sw128(st + 2 * LT_A_BYTES);   // W_hi rows, then W_lo rows
-                    const uint64_t d_blo = umma_desc_sw128(st + 2 * LT_A_BYTES + B_BYTES);
 #pragma unroll
                     for (int ks = 0; ks < LT_KB / 8; ++ks, ++step) {   // +32 bytes per K=8 step inside the swizzled row
                         const uint64_t o = (uint64_t)(2 * ks);
-                        if (SHARED_L) {
-                            const uint32_t d_h = acc + (uint32_t)((step % LT_ACC) * BN), d_l = acc + (uint32_t)(LT_ACC * BN);
-                            tcgen05_mma_tf32(d_h, d_ahi + o, d_b + o, idesc_lo, (uint32_t)(step >= LT_ACC));
-                            tcgen05_mma_tf32(d_l, d_ahi + o, d_blo + o, idesc_lo, (uint32_t)(step > 0));
-                            tcgen05_mma_tf32(d_l, d_alo + o, d_b + o, idesc_lo, 1u);
-                        } else {
-                            const uint32_t d = acc + (uint32_t)((step % LT_ACC) * 2 * BN);
-                            tcgen05_mma_tf32(d, d_ahi + o, d_b + o, idesc_wide, (uint32_t)(step >= LT_ACC));
-                            tcgen05_mma_tf32(d + BN, d_alo + o, d_b + o, idesc_lo, 1u);
-                        }
+                        const uint32_t d = acc + (uint32_t)((step % LT_ACC) * 2 * BN);
+                        tcgen05_mma_tf32(d, d_ahi + o, d_b + o, idesc_wide, (uint32_t)(step >= LT_ACC));
+                        tcgen05_mma_tf32(d + BN, d_alo + o, d_b + o, idesc_lo, 1u);
                     }
                     tcgen05_commit(&empty[s]);
                     if (++s == NSTAGE) { s = 0; phase ^= 1u; }
@@ -220,6 +215,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 float4* a_lo = a_hi + LT_A_BYTES / 16;
 #pragma unroll
                 for (int i = 0; i < LT_A_BYTES / 16 / 128; ++i) {
+                    if (i * 16 >= bm) break;               // 16 rows per pass; rows >= bm are not loaded
                     const float4 v = a_hi[t + i * 128];
                     float4 h, l;
                     split_rn(v.x, h.x, l.x); split_rn(v.y, h.y, l.y);
@@ -238,12 +234,90 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         const int quarter = warp & 3;                  // TMEM lanes this warp may read
         uint8_t* my_stage = out_stage + (warp - 6) * LT_OUT_BYTES;
         int it = 0;
-        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, it += (RANGE > 0 ? 0 : 1)) {
             const int buf = it % NBUF, use = it / NBUF;
-            const long long m0 = (long long)(tile / n_tiles_n) * LT_BM;
+            const long long m0 = (long long)(tile / n_tiles_n) * bm;
+            const bool idle = !DENSE && quarter * 32 >= bm;   // this warp's 32 rows lie beyond the tile
             const int n0 = (tile % n_tiles_n) * BN;
+            const long long row0 = m0 + quarter * 32, row = row0 + lane;
+            // bias + ReLU on one 32-column chunk of this thread's row, then out through TMA or plain stores
+            auto finish = [&](int cb, float (&r)[32]) {
+                const int c0 = n0 + cb;
+                if (bias && row < bias_rows) {       // the bias may apply to the leading rows only
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) r[j] += (c0 + j < n_out) ? __ldg(bias + c0 + j) : 0.f;
+                }
+                if (relu) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) r[j] = fmaxf(r[j], 0.f);
+                }
+                if (y_tma) {
+                    // registers -> swizzled staging rows (conflict-free 128-bit stores) -> one TMA
+                    // store of the 32 x 32 box, which writes whole 128-byte row segments and clips
+                    // rows / columns beyond the matrix
+                    if (row0 < rows) {
+                        if (lane == 0) tma_store_wait_read();
+                        __syncwarp();
+#pragma unroll
+                        for (int j = 0; j < 8; ++j)
+                            *reinterpret_cast<float4*>(my_stage + lane * 128 + ((j ^ (lane & 7)) << 4)) =
+                                make_float4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+                        fence_proxy_async_smem();
+                        __syncwarp();
+                        if (lane == 0) {
+                            tma_store_2d(&map_y, my_stage, c0, (int)row0);
+                            tma_store_commit();
+                        }
+                    }
+                } else if (row < rows) {
+                    float* dst = y + row * ldy + c0;
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (c0 + j < n_out) dst[j] = r[j];
+                }
+            };
+            if (RANGE > 0) {
+                static_assert(RANGE == 0 || (!DENSE && LT_ACC == 1), "ranges drain [H | L] sets");
+                float sum[BN / 32][32];
+#pragma unroll
+                for (int c = 0; c < BN / 32; ++c)
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) sum[c][j] = 0.f;
+                for (int kb0 = 0; kb0 < k_blocks; kb0 += RANGE, ++it) {
+                    const int rbuf = it % NBUF, ruse = it / NBUF;
+                    mbar_wait(&acc_full[rbuf], (uint32_t)(ruse & 1));
+                    tcgen05_fence_after();
+                    if (idle) {
+                        tcgen05_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(&acc_empty[rbuf]);
+                        continue;
+                    }
+                    const uint32_t lane_base = tmem_d + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(rbuf * ACC_COLS);
+#pragma unroll
+                    for (int c = 0; c < BN / 16; ++c) {      // 16 columns at a time: 128 running sums stay in registers
+                        float h[16], l[16];
+                        tmem_ld_32x32b_x16_pair(lane_base + (uint32_t)(c * 16), lane_base + (uint32_t)(BN + c * 16), h, l);
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) sum[c / 2][(c % 2) * 16 + j] += h[j] + l[j];
+                    }
+                    tcgen05_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&acc_empty[rbuf]);
+                }
+#pragma unroll
+                for (int c = 0; c < BN / 32; ++c)
+                    if (!idle && n0 + c * 32 < n_out) finish(c * 32, sum[c]);
+                continue;
+            }
             mbar_wait(&acc_full[buf], (uint32_t)(use & 1));
             tcgen05_fence_after();
+            if (idle) {
+                tcgen05_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&acc_empty[buf]);
+                continue;
+            }
             if (DENSE) {
                 // ---- masked row softmax of this row's n_s x n_t block, straight out of TMEM ----
                 const int r = quarter * 32 + lane;                 // row of the tile
@@ -313,28 +387,11 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 }
                 continue;
             }
-            const long long row0 = m0 + quarter * 32, row = row0 + lane;
 #pragma unroll 1
             for (int cb = 0; cb < BN; cb += 32) {
                 if (n0 + cb >= n_out) break;               // warp-uniform; cb = 0 is always live
                 float r[32];
-                if (SHARED_L) {
-                    // H_0 + H_1 + ... + L, two TMEM loads per wait (LT_ACC + 1 is even), the small L last
-                    static_assert(!SHARED_L || (LT_ACC + 1) % 2 == 0, "accumulators are read in pairs");
-                    const uint32_t lane_base = tmem_d + ((uint32_t)(quarter * 32) << 16) +
-                                               (uint32_t)(buf * ACC_COLS + cb);
-                    float q[32];
-                    tmem_ld_32x32b_x32_pair(lane_base, lane_base + (uint32_t)BN, r, q);
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) r[j] += q[j];
-#pragma unroll
-                    for (int a = 2; a < LT_ACC + 1; a += 2) {
-                        float p2[32];
-                        tmem_ld_32x32b_x32_pair(lane_base + (uint32_t)(a * BN), lane_base + (uint32_t)((a + 1) * BN), p2, q);
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) r[j] = (r[j] + p2[j]) + q[j];
-                    }
-                } else {
+                {
                     const uint32_t lane_base = tmem_d + ((uint32_t)(quarter * 32) << 16) +
                                                (uint32_t)(buf * ACC_COLS + cb);
                     float l[32];
@@ -355,39 +412,7 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&acc_empty[buf]);
                 }
-                const int c0 = n0 + cb;
-                if (bias && row < bias_rows) {       // the bias may apply to the leading rows only
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) r[j] += (c0 + j < n_out) ? __ldg(bias + c0 + j) : 0.f;
-                }
-                if (relu) {
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) r[j] = fmaxf(r[j], 0.f);
-                }
-                if (y_tma) {
-                    // registers -> swizzled staging rows (conflict-free 128-bit stores) -> one TMA
-                    // store of the 32 x 32 box, which writes whole 128-byte row segments and clips
-                    // rows / columns beyond the matrix
-                    if (row0 < rows) {
-                        if (lane == 0) tma_store_wait_read();
-                        __syncwarp();
-#pragma unroll
-                        for (int j = 0; j < 8; ++j)
-                            *reinterpret_cast<float4*>(my_stage + lane * 128 + ((j ^ (lane & 7)) << 4)) =
-                                make_float4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
-                        fence_proxy_async_smem();
-                        __syncwarp();
-                        if (lane == 0) {
-                            tma_store_2d(&map_y, my_stage, c0, (int)row0);
-                            tma_store_commit();
-                        }
-                    }
-                } else if (row < rows) {
-                    float* dst = y + row * ldy + c0;
-#pragma unroll
-                    for (int j = 0; j < 32; ++j)
-                        if (c0 + j < n_out) dst[j] = r[j];
-                }
+                finish(cb, r);
             }
         }
         if (lane == 0) tma_store_wait_all();
@@ -438,17 +463,17 @@ static int lt_make_map(CUtensorMap* map, const void* base, long long rows, long 
 static int lt_bn(int n_out) { return n_out <= 64 ? 64 : 128; }
 static int lt_round(int v, int m) { return (v + m - 1) / m * m; }
 
-template <int BN, int ACC, bool SHARED_L = false>
+template <int BN, int ACC, int RANGE = 0>
 static int lt_launch(const CUtensorMap& mx, const CUtensorMap& mh, const CUtensorMap& ml,
                      const CUtensorMap& my, int y_tma, const float* bias, long long bias_rows, int relu, float* y, long long ldy, long long rows, int n_out, int k_blocks, int n_pad,
-                     cudaStream_t stream) {
+                     int bm, cudaStream_t stream) {
     const DenseArgs no_dense = {};
     constexpr int STAGE = 2 * LT_A_BYTES + 2 * BN * LT_KB * 4;
     // the full ring always (>= 192 KB): one CTA per SM, which owns all 512 TMEM columns
     const size_t smem = (size_t)lt_stages(BN) * STAGE + 4 * LT_OUT_BYTES + (3 * LT_MAX_STAGES + 6) * 8 + 1024;
     static DeviceOnce configured;
     if (!configured.done()) {
-        if (cudaFuncSetAttribute(linear_tc_kernel<BN, ACC, false, SHARED_L>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        if (cudaFuncSetAttribute(linear_tc_kernel<BN, ACC, false, RANGE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)smem) != cudaSuccess) {
             set_error("linear_tc: cannot set %zu bytes of dynamic shared memory", smem);
             return DGMC_ERR_CUDA;
@@ -456,12 +481,12 @@ static int lt_launch(const CUtensorMap& mx, const CUtensorMap& mh, const CUtenso
         configured.mark();
     }
     const int n_tiles_n = n_pad / BN;
-    const long long tiles = (long long)n_tiles_n * ((rows + LT_BM - 1) / LT_BM);
+    const long long tiles = (long long)n_tiles_n * ((rows + bm - 1) / bm);
     if (tiles > 0x7fffffffLL) { set_error("linear_tc: too many tiles"); return DGMC_ERR_UNSUPPORTED; }
     const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
-    linear_tc_kernel<BN, ACC, false, SHARED_L><<<grid, LT_THREADS, smem, stream>>>(mx, mh, ml, my, y_tma, bias, bias_rows, relu, y,
+    linear_tc_kernel<BN, ACC, false, RANGE><<<grid, LT_THREADS, smem, stream>>>(mx, mh, ml, my, y_tma, bias, bias_rows, relu, y,
                                                                    ldy, rows, n_out, k_blocks, n_tiles_n, (int)tiles,
-                                                                   no_dense);
+                                                                   bm, no_dense);
     return DGMC_OK;
 }
 
@@ -510,18 +535,34 @@ static int linear_tc_impl(const float* x, int64_t ldx, const void* split_weight,
                   "aligned base and pitch)", (long long)rows, n_out, k_in, (long long)ldx);
         return DGMC_ERR_UNSUPPORTED;
     }
-    // the split weight is padded to lt_bn(n_out) rows (workspace layout); long reductions (more than 12
-    // k blocks: psi_1's 768 ... 1068 columns) run on 64-column tiles whatever n_out is, so that seven H
-    // accumulators fit into TMEM — every accumulator then sees <= ~20 truncating adds.  Measured on psi_1
-    // at the DBP15K shape against fp64: 7.4e-7 of max|h| (IEEE fp32 on the CPU: 8.4e-7; two pairs on
-    // 128-column tiles: 2.4e-6), at 1.8x the time of those GEMMs (+0.33 ms per DBP15K training step).
+    // Long reductions (more than 12 k blocks: psi_1's 768 ... 1068 columns) run in ranges of 4 k blocks
+    // whose accumulator sets the epilogue drains into register sums (RANGE in the kernel): 16 truncating
+    // adds per TMEM accumulator whatever k_in is.  Measured on psi_1 at the DBP15K shape against fp64:
+    // 6.1e-7 of max|h| (IEEE fp32 on the CPU: 8.4e-7; two accumulator pairs over the whole reduction:
+    // 2.4e-6, which put S_0 5x further from fp64 than the reference's own fp32 noise), at 99 us instead
+    // of 93 us for 34.5 k x 900 -> 256.
     const int n_pad = tc::lt_round(n_out, tc::lt_bn(n_out)), k_pad = tc::lt_round(k_in, tc::LT_KB);
     const bool long_k = k_pad / tc::LT_KB > 12;
-    const int bn = long_k ? 64 : tc::lt_bn(n_out);
+    const int bn = tc::lt_bn(n_out);
     const float* hi = static_cast<const float*>(split_weight);
     const float* lo = hi + (size_t)n_pad * k_pad;
+    // Rows per tile: the persistent CTAs work through ceil(tiles / SMs) rounds, and the last round is
+    // mostly idle when the tile count sits just above a multiple of the SM count (38,960 rows = 305
+    // tiles of 128 on 148 SMs: three rounds for 2.06 rounds of work).  The MMA is not the limit of
+    // these GEMMs, so a tile may as well hold only 96 or 64 live rows of the M = 128 instruction when
+    // that shortens the critical path by >= 10 % (a tile costs about 48 rows' worth of fixed time;
+    // measured: 38,960 x 192 -> 64: 18.6 -> 16.5 us with 96 rows; 257 x 72 -> 50: 9.3 -> 6.8 us with 64;
+    // where the model predicts less, e.g. 35,000 rows or two column tiles, shorter tiles measured slower).
+    int bm = tc::LT_BM;
+    {
+        const long long sms = sm_count(), n_tiles_n = n_pad / bn;
+        auto path = [&](int h) { return ((n_tiles_n * ((rows + h - 1) / h) + sms - 1) / sms) * (h + 48); };
+        long long best = path(tc::LT_BM);
+        for (int cand = 96; cand >= 64; cand -= 32)
+            if (10 * path(cand) <= 9 * best) { best = path(cand); bm = cand; }
+    }
     CUtensorMap mx, mh, ml;
-    if (int e = tc::lt_make_map(&mx, x, rows, k_in, ldx, tc::LT_BM)) return e;
+    if (int e = tc::lt_make_map(&mx, x, rows, k_in, ldx, bm)) return e;
     if (int e = tc::lt_make_map(&mh, hi, n_pad, k_pad, k_pad, bn)) return e;
     if (int e = tc::lt_make_map(&ml, lo, n_pad, k_pad, k_pad, bn)) return e;
     // y through TMA stores when its base and pitch are 16-byte aligned, else plain stores
@@ -532,8 +573,8 @@ static int linear_tc_impl(const float* x, int64_t ldx, const void* split_weight,
     const int k_blocks = k_pad / tc::LT_KB;
     int e;
     const bool short_k = k_blocks <= 4;
-#define DGMC_LT_ARGS mx, mh, ml, my, y_tma, bias, bias_rows, relu, y, ldy, rows, n_out, k_blocks, n_pad, stream
-    if (long_k) e = tc::lt_launch<64, 7, true>(DGMC_LT_ARGS);
+#define DGMC_LT_ARGS mx, mh, ml, my, y_tma, bias, bias_rows, relu, y, ldy, rows, n_out, k_blocks, n_pad, bm, stream
+    if (long_k) e = bn == 64 ? tc::lt_launch<64, 1, 4>(DGMC_LT_ARGS) : tc::lt_launch<128, 1, 4>(DGMC_LT_ARGS);
     else if (bn == 64) e = short_k ? tc::lt_launch<64, 1>(DGMC_LT_ARGS) : tc::lt_launch<64, 2>(DGMC_LT_ARGS);
     else          e = short_k ? tc::lt_launch<128, 1>(DGMC_LT_ARGS) : tc::lt_launch<128, 2>(DGMC_LT_ARGS);
 #undef DGMC_LT_ARGS
@@ -615,6 +656,6 @@ extern "C" int dgmc_dense_scores_tc(const float* h_s, const float* h_t, const ui
     }
     const int grid = tiles < sm_count() ? tiles : sm_count();
     tc::linear_tc_kernel<128, 2, true><<<grid, tc::LT_THREADS, smem, stream>>>(
-        mx, mh, ml, mx, 0, nullptr, 0, 0, nullptr, 0, (long long)B * n_s, 128, k_pad / tc::LT_KB, 1, tiles, d);
+        mx, mh, ml, mx, 0, nullptr, 0, 0, nullptr, 0, (long long)B * n_s, 128, k_pad / tc::LT_KB, 1, tiles, tc::LT_BM, d);
     return check_launch("dense_scores_tc");
 }

@@ -19,7 +19,7 @@ def run(x, w, b, relu, trans=False):
     y = torch.empty(rows, n_out, device=dev)
     call('dgmc_linear_tc', RowStrided(x), x.stride(0), ws, b, int(relu), y, n_out, rows, n_out, k_in, stream_ptr())
     return y, ws
-for rows, n_out, k_in, relu, trans in [(257, 50, 72, True, False), (35000, 64, 192, True, False), (35000, 64, 256, False, True), (35000, 192, 64, False, True), (35000, 256, 64, False, True),
+for rows, n_out, k_in, relu, trans in [(257, 50, 72, True, False), (38960, 64, 192, True, False), (38960, 192, 64, False, True), (35000, 64, 192, True, False), (35000, 64, 256, False, True), (35000, 192, 64, False, True), (35000, 256, 64, False, True),
                                        (34500, 256, 900, True, False), (34500, 256, 1068, False, False), (34500, 768, 256, False, True),
                                        (10000, 6400, 256, False, False)]:
     x = torch.randn(rows, k_in, device=dev)

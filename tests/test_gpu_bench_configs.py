@@ -167,8 +167,9 @@ def test_configs2_full_dbp15k_training_step_against_oracle():
     The logits <h_s, h_t> reach ~150 here (one fp32 ulp of them is 1.5e-5, which is why those fp32
     evaluations are 1.6e-5 / 2.0e-5 off fp64), and h comes out of psi_1's K = 900 / 768 / 1068 GEMMs,
     which run as 3xTF32 on the tensor cores.  The TMEM accumulator truncates on every add, so those
-    long reductions are spread over seven accumulators (linear_tc.cu, SHARED_L): 7.4e-7 of max|h|
-    against 8.4e-7 for an IEEE fp32 GEMM (profiles/diag_s0_error.py).  Measured: S_0 2.2e-5,
+    long reductions are cut into 128-column ranges whose accumulators the epilogue drains into
+    register sums (linear_tc.cu, RANGE): 6.1e-7 of max|h| against 8.4e-7 for an IEEE fp32 GEMM
+    (profiles/diag_s0_error.py).  Measured: S_0 2.2e-5,
     S_L 3.0e-5, printed by the test."""
     _training_step_parity(n_s=19388, n_t=19572, feat=300, dim=256, R=64, layers=3, k=10, steps=10,
                           n_pairs=4500, e_s_count=70414, e_t_count=95142, dropout=0.5, seed=0,
