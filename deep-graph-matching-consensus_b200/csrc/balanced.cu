@@ -360,10 +360,10 @@ __global__ void __launch_bounds__(256) balanced_fixup_kernel(const BalArgs a, in
         if (s_next2 == s) {
             // A hub: the segment runs on over many blocks (a target node that sits in thousands of
             // candidate lists: 100+ pieces).  Its last block follows from `ptr`, so the pieces are
-            // loaded U at a time — independent loads, all in flight together — and added in block
+            // loaded U = 32 / NV at a time — independent loads, all in flight together — and added in block
             // order, exactly as a one-by-one walk would add them (a chain of 100+ dependent L2 round
             // trips otherwise: 34 us per launch at the DBP15K shape, ncu).
-            constexpr int U = 16 / NV;
+            constexpr int U = 32 / NV;
             const long long b_last = ((long long)__ldg(a.ptr + s + 1) - 1) / CB;
             for (long long bb = b + 2; bb <= b_last; bb += U) {
                 float4 t[U][NV];

@@ -215,7 +215,9 @@ linear_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 float4* a_lo = a_hi + LT_A_BYTES / 16;
 #pragma unroll
                 for (int i = 0; i < LT_A_BYTES / 16 / 128; ++i) {
-                    if (i * 16 >= bm) break;               // 16 rows per pass; rows >= bm are not loaded
+                    // all 128 rows, whatever bm is: rows >= bm hold stale values whose products land in
+                    // accumulator rows nobody reads — a test on bm here costs the eight independent loads
+                    // their overlap (measured: 15.1 -> 18.5 us at 38,960 x 192 -> 64)
                     const float4 v = a_hi[t + i * 128];
                     float4 h, l;
                     split_rn(v.x, h.x, l.x); split_rn(v.y, h.y, l.y);
@@ -546,20 +548,16 @@ static int linear_tc_impl(const float* x, int64_t ldx, const void* split_weight,
     const int bn = tc::lt_bn(n_out);
     const float* hi = static_cast<const float*>(split_weight);
     const float* lo = hi + (size_t)n_pad * k_pad;
-    // Rows per tile: the persistent CTAs work through ceil(tiles / SMs) rounds, and the last round is
-    // mostly idle when the tile count sits just above a multiple of the SM count (38,960 rows = 305
-    // tiles of 128 on 148 SMs: three rounds for 2.06 rounds of work).  The MMA is not the limit of
-    // these GEMMs, so a tile may as well hold only 96 or 64 live rows of the M = 128 instruction when
-    // that shortens the critical path by >= 10 % (a tile costs about 48 rows' worth of fixed time;
-    // measured: 38,960 x 192 -> 64: 18.6 -> 16.5 us with 96 rows; 257 x 72 -> 50: 9.3 -> 6.8 us with 64;
-    // where the model predicts less, e.g. 35,000 rows or two column tiles, shorter tiles measured slower).
+    // Rows per tile: 128, except for matrices too small to give every SM a tile — there a tile holds only
+    // 96 or 64 live rows of the M = 128 instruction (the MMA is not the limit of these GEMMs), so that
+    // more SMs take part: 257 x 72 -> 50: 8.8 -> 7.0 us.  With more than one round of tiles shorter tiles
+    // measured level or slower (38,960 x 192 -> 64: 15.1 us with 128 rows, 15.5 us with 96), so the rule
+    // stops there.
     int bm = tc::LT_BM;
     {
         const long long sms = sm_count(), n_tiles_n = n_pad / bn;
-        auto path = [&](int h) { return ((n_tiles_n * ((rows + h - 1) / h) + sms - 1) / sms) * (h + 48); };
-        long long best = path(tc::LT_BM);
-        for (int cand = 96; cand >= 64; cand -= 32)
-            if (10 * path(cand) <= 9 * best) { best = path(cand); bm = cand; }
+        auto tiles = [&](int h) { return n_tiles_n * ((rows + h - 1) / h); };
+        if (tiles(tc::LT_BM) < sms) bm = tiles(64) <= sms ? 64 : (tiles(96) <= sms ? 96 : tc::LT_BM);
     }
     CUtensorMap mx, mh, ml;
     if (int e = tc::lt_make_map(&mx, x, rows, k_in, ldx, bm)) return e;
