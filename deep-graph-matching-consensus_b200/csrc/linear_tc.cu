@@ -18,8 +18,10 @@
 //   warp 1      one thread issues, per k8 step, X_hi x [W_hi ; W_lo] (N = 2 BN) and X_lo x W_hi
 //               (N = BN) as tcgen05.mma.kind::tf32; tcgen05.commit releases the stage to the producer
 //   warps 6-9   epilogue: tcgen05.ld of the accumulator rows (summing the accumulator pairs),
-//               + bias, ReLU, swizzled staging rows, one TMA store per 32 x 32 box; at BN = 64 there are two accumulator sets, so the
-//               epilogue of one tile overlaps the MMAs of the next
+//               + bias, ReLU, swizzled staging rows, one TMA store per 32 x 32 box; with two
+//               accumulator sets in TMEM the epilogue of one tile overlaps the MMAs of the next.
+//               Reductions longer than 384 columns are cut into ranges of 128 whose accumulator sets
+//               these warps drain into register sums (the TMEM accumulate truncates: see RANGE)
 // Rows and k beyond the matrix are zero-filled by TMA (X) or by the padded workspace (W).
 #include <cstring>
 #include "common.cuh"

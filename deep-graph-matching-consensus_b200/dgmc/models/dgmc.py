@@ -175,7 +175,7 @@ class DGMC(torch.nn.Module):
             w1, b1, w2 = F.pad(w1, (0, 0, 0, pad)), F.pad(b1, (0, pad)), F.pad(w2, (0, pad))
         return w1, b1, w2, b2
 
-    def _psi_2_then_lin1(self, x0, merged, w1, b1, n_source):
+    def _psi_2_then_lin1(self, x0, merged, w1, b1, n_source, buffer=None):
         """P = Lin1(psi_2(x0)) on the merged node table, with b1 on the source rows only.  When
         psi_2 ends in its own Lin (RelCNN(lin=True)), the two linear maps have nothing in between:
         P = feats (W1 W_f)^T + W1 b_f (+ b1), one GEMM instead of two (and one input-gradient and
@@ -186,7 +186,7 @@ class DGMC(torch.nn.Module):
         from .rel import RelCNN
         psi = self.psi_2
         if isinstance(psi, RelCNN) and psi.lin:
-            feats = psi(x0, merged.edge_index, merged.edge_attr, features_only=True)
+            feats = psi(x0, merged.edge_index, merged.edge_attr, features_only=True, buffer=buffer)
             w_eff, b_eff = ops.region_cached(('lin1_final', id(self)), lambda: (
                 w1 @ psi.final.weight, b1 + 0.0 * (w1 @ psi.final.bias)))
             return ops.node_linear(feats, w_eff, b_eff, key=('lin1_final', id(self)), bias_rows=n_source)
@@ -280,6 +280,8 @@ class DGMC(torch.nn.Module):
         S_hat = ops.gather_dot(h_s.reshape(B * N_s, C), h_t.reshape(B * N_t, C), cand)
         S_0 = _rows(ops.softmax_k(S_hat), s_lay)
         one_pair = merged is not None and s_mask is None and t_mask is None
+        from .rel import RelCNN
+        direct_psi_2 = one_pair and isinstance(self.psi_2, RelCNN) and self.psi_2.lin
         for _ in range(num_steps):
             S = ops.softmax_k(S_hat)
             if one_pair:
@@ -288,13 +290,19 @@ class DGMC(torch.nn.Module):
                 # one tensor.  The indicators are drawn, and the transport is written, straight into
                 # that table (no concatenation).  b1 belongs to the source rows: added by the GEMM
                 # epilogue, its gradient summed by the weight-gradient kernel.
-                x0 = torch.empty(B * N_s + cand.targets, R_in, dtype=h_s.dtype, device=h_s.device)
+                # ... and that table is the leading column block of psi_2's concatenated feature
+                # table where psi_2 can work in one (RelCNN(cat=True, lin=True) without batch norm /
+                # dropout): psi_2 then does not copy its input either
+                fb = self.psi_2.feature_buffer(B * N_s + cand.targets, h_s.device) \
+                    if direct_psi_2 and h_s.dtype == torch.float32 else None
+                x0 = fb[:, :R_in] if fb is not None else \
+                    torch.empty(B * N_s + cand.targets, R_in, dtype=h_s.dtype, device=h_s.device)
                 top = x0[:B * N_s]
                 r_s = torch.randn((B, N_s, R_in), dtype=h_s.dtype, device=h_s.device, out=top.view(B, N_s, R_in))
                 if r_s.data_ptr() != top.data_ptr():      # a replayed draw (tests): copy it in
                     top.copy_(r_s.reshape(B * N_s, R_in))
                 r_t = ops.transport(S, top, cand, out=x0[B * N_s:])
-                p = self._psi_2_then_lin1(ops.join_rows(x0, top, r_t), merged, w1, b1, B * N_s)
+                p = self._psi_2_then_lin1(ops.join_rows(x0, top, r_t), merged, w1, b1, B * N_s, buffer=fb)
                 S_hat = ops.diff_mlp_merged(S_hat, p, B * N_s, None, w2, b2, cand)
                 continue
             r_s = torch.randn((B, N_s, R_in), dtype=h_s.dtype, device=h_s.device)

@@ -86,10 +86,26 @@ class RelCNN(torch.nn.Module):
                 and x.is_cuda and x.dtype == torch.float32 and x.dim() == 2
                 and self.in_channels % 4 == 0 and self.convs[0].out_channels % 4 == 0)
 
-    def _forward_direct(self, x, edge_index, features_only=False):
+    def feature_buffer(self, n, device):
+        """An empty [n, in + L*out] table for `forward(..., buffer=)`: a caller that PRODUCES the input
+        (DGMC writes the indicators and their transport) can write it straight into the leading column
+        block `buffer[:, :in_channels]` and save the copy.  None when the layers cannot write into one
+        concatenated table (see _direct_cat)."""
+        probe = torch.empty(0, self.in_channels, dtype=torch.float32, device=device)
+        if not self._direct_cat(probe):
+            return None
+        return torch.empty(n, self.in_channels + self.num_layers * self.convs[0].out_channels,
+                           dtype=torch.float32, device=device)
+
+    def _forward_direct(self, x, edge_index, features_only=False, buffer=None):
         c_in, c_out = self.in_channels, self.convs[0].out_channels
-        buf = torch.empty(x.size(0), c_in + self.num_layers * c_out, dtype=torch.float32, device=x.device)
-        cur, parts, off = ops.copy_into(x, buf, 0), [], c_in
+        if buffer is not None and x.data_ptr() == buffer.data_ptr() and x.stride(0) == buffer.stride(0) \
+                and x.size(0) == buffer.size(0) and buffer.size(1) == c_in + self.num_layers * c_out:
+            buf, cur = buffer, x                      # x already IS the leading column block
+        else:
+            buf = torch.empty(x.size(0), c_in + self.num_layers * c_out, dtype=torch.float32, device=x.device)
+            cur = ops.copy_into(x, buf, 0)
+        parts, off = [], c_in
         for conv in self.convs:
             cur, alias = conv(cur, edge_index, relu=True, out=buf[:, off:off + c_out], passthrough=True)
             parts.append(alias)
@@ -102,13 +118,13 @@ class RelCNN(torch.nn.Module):
             return out
         return ops.node_linear(out, self.final.weight, self.final.bias, key=('final', id(self)))
 
-    def forward(self, x, edge_index, *args, features_only=False):
+    def forward(self, x, edge_index, *args, features_only=False, buffer=None):
         """features_only: return the input of the final Lin (the concatenated layer outputs) instead
         of applying it — DGMC folds that Lin into the first consensus-MLP layer (two linear maps
-        with nothing in between)."""
+        with nothing in between).  buffer: see feature_buffer()."""
         assert not features_only or self.lin
         if self._direct_cat(x):
-            return self._forward_direct(x, edge_index, features_only)
+            return self._forward_direct(x, edge_index, features_only, buffer)
         feats = [x]
         for conv, norm in zip(self.convs, self.batch_norms):
             h = conv(feats[-1], edge_index, relu=True)

@@ -371,10 +371,11 @@ def masked_softmax(x, s_mask_u8, t_mask_u8):
 # K2
 # --------------------------------------------------------------------------------------------
 def _gather_dot_raw(a, b, idx):
+    """a, b: fp32 rows with unit column stride (any row pitch)."""
     m, k = idx.shape
     out = torch.empty(m, k, dtype=torch.float32, device=a.device)
-    call('dgmc_gather_dot_fwd', a, a.stride(0), b, b.stride(0), idx, out, m, k, a.size(1),
-         stream_ptr())
+    call('dgmc_gather_dot_fwd', RowStrided(a), a.stride(0), RowStrided(b), b.stride(0), idx, out, m, k,
+         a.size(1), stream_ptr())
     return out
 
 
@@ -411,7 +412,7 @@ def gather_dot(a, b, cand):
 class _Transport(torch.autograd.Function):
     @staticmethod
     def forward(ctx, S, r_s, cand, out):
-        S, r_s = _f32(S), _f32(r_s)
+        S, r_s = _f32(S), _rows_f32(r_s)       # r_s may be a row block of a wider table (row pitch > R)
         tptr, perm, seg_of = cand.csr
         ctx.cand = cand
         ctx.save_for_backward(S, r_s)
@@ -421,7 +422,9 @@ class _Transport(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g):
         S, r_s = ctx.saved_tensors
-        cand, g = ctx.cand, _f32(g)
+        # g may be a row block of a wider gradient buffer (psi_2's concatenated features): both kernels
+        # below take a row pitch, so no contiguous copy
+        cand, g = ctx.cand, _rows_f32(g)
         dS = dr = None
         if ctx.needs_input_grad[0]:  # dS[m, j] = <r_s[m], g[idx[m, j]]>
             dS = _gather_dot_raw(r_s, g, cand.idx)

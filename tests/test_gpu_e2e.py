@@ -102,3 +102,19 @@ def test_training_step_is_bit_reproducible():
     assert torch.equal(a['loss_L'], b['loss_L'])
     for name, grad in a['grads'].items():
         assert torch.equal(grad, b['grads'][name]), name
+
+
+def test_randn_into_row_strided_table_draws_the_contiguous_stream():
+    """DGMC draws the indicators straight into the leading column block of psi_2's feature table (rows
+    256 floats apart): the values must be the ones `torch.randn((B, N_s, R))` gives for the same seed —
+    the RNG contract with the reference (dgmc.py:206,228)."""
+    n, r, width = 19388, 64, 256
+    torch.cuda.manual_seed(123)
+    ref = torch.randn((1, n, r), device='cuda')
+    table = torch.zeros(n + 100, width, device='cuda')
+    torch.cuda.manual_seed(123)
+    top = table[:n, :r]
+    out = torch.randn((1, n, r), device='cuda', out=top.view(1, n, r))
+    assert out.data_ptr() == table.data_ptr()
+    assert torch.equal(table[:n, :r], ref[0])
+    assert float(table[:, r:].abs().max()) == 0.0 and float(table[n:].abs().max()) == 0.0
