@@ -62,7 +62,7 @@ def _sum_over_ranks(x, group, keep=True):
     n = x.numel()
     src = pc.scratch_in(1, n)
     if x.data_ptr() != src.data_ptr():       # the producer may already have written into the scratch
-        src.copy_(x.reshape(1, n))
+        src.view(x.shape).copy_(x)           # (one copy also when x is a strided block of a wider table)
     y = pc.all_reduce(1, n)
     return (y.clone() if keep else y).view(x.shape)
 
@@ -366,9 +366,24 @@ class RowShardedDGMC(DGMC):
         k = cand.k
         S_hat = ops.gather_dot(h_loc, h_t, cand)
         S_0 = ops.softmax_k(S_hat)
+        from .rel import RelCNN
+        direct_psi_2 = sp is None and merged is not None and isinstance(self.psi_2, RelCNN) and self.psi_2.lin \
+            and h_t.dtype == torch.float32
         for _ in range(num_steps):
             S = ops.softmax_k(S_hat)
-            r_s = torch.randn((1, N_s, R_in), dtype=h_t.dtype, device=h_t.device).view(N_s, R_in)
+            # replicated psi_2 = RelCNN: the merged node table [r_s ; r_t] is the leading column block of
+            # psi_2's concatenated feature table — the draw goes straight into it (same stream as a
+            # contiguous draw), the all-reduced transport is copied in once; no cat, no input copy
+            fb = self.psi_2.feature_buffer(N_s + N_t, h_t.device) if direct_psi_2 else None
+            if fb is not None:
+                x0 = fb[:, :R_in]
+                top = x0[:N_s]
+                r_s = torch.randn((1, N_s, R_in), dtype=h_t.dtype, device=h_t.device, out=top.view(1, N_s, R_in))
+                if r_s.data_ptr() != top.data_ptr():      # a replayed draw (tests): copy it in
+                    top.copy_(r_s.reshape(N_s, R_in))
+                r_s = top
+            else:
+                r_s = torch.randn((1, N_s, R_in), dtype=h_t.dtype, device=h_t.device).view(N_s, R_in)
             # the partial transport goes straight into the buffer the peers' all-reduce kernels read
             part = transport_partial_buffer(N_t, R_in, h_t.device, self.group)
             # (r_t is consumed by the concatenation below before the next collective: no copy out)
@@ -385,7 +400,11 @@ class RowShardedDGMC(DGMC):
             # psi_2 replicated on the merged pair (this package's RelCNN / SplineCNN without batch-norm
             # statistics or dropout); K6 on this rank's source rows of the merged node table
             assert merged is not None, 'RowShardedDGMC needs a psi_2 that runs on the merged pair'
-            p = self._psi_2_then_lin1(torch.cat([r_s, r_t], dim=0), merged, w1, b1, N_s)
+            if fb is not None:
+                table = ops.join_rows(x0, top, ops.copy_to(r_t, x0[N_s:]))
+            else:
+                table = torch.cat([r_s, r_t], dim=0)
+            p = self._psi_2_then_lin1(table, merged, w1, b1, N_s, buffer=fb)
             S_hat = ops.diff_mlp_merged(S_hat, p, N_s, None, w2, b2, cand, rows=(lo, hi))
         S_L = ops.softmax_k(S_hat)
         S_idx = S_idx.view(n_loc, k)

@@ -985,6 +985,24 @@ class _CopyInto(torch.autograd.Function):
         return g, None, None
 
 
+class _CopyTo(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, dst):
+        # through .data: the table's version counter must not move — other row blocks of the same table
+        # (disjoint from dst) may already be saved for a backward pass
+        dst.data.copy_(x)
+        return dst.view_as(dst)
+
+    @staticmethod
+    def backward(ctx, g):
+        return g, None
+
+
+def copy_to(x, dst):
+    """dst[...] = x for a pre-allocated block `dst` of a larger table; returns dst (gradient: identity)."""
+    return _CopyTo.apply(x, dst)
+
+
 def copy_into(x, buf, offset):
     """buf[:, offset : offset + x.size(1)] = x; returns that column block (gradient: identity)."""
     return _CopyInto.apply(x, buf, offset)
