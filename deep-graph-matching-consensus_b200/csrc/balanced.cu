@@ -316,74 +316,24 @@ __global__ void __launch_bounds__(256, 5) balanced_lean_kernel(const BalArgs a) 
 }
 
 // One lane group per entry block: if the block holds the FIRST piece of a segment that runs on into
-// later blocks, add that segment's pieces up in block order and write the result.
+// later blocks, add that segment's pieces up in block order and write the result.  A HUB (a target node
+// that sits in thousands of candidate lists: 100+ pieces) is not walked by its one group — a chain of
+// dependent L2 round trips, 34 us per launch at the DBP15K shape and 60 us on a hub-heavy edge list —
+// but handed to the whole CTA: group g adds the pieces g, g + GPC, ... and the first group adds the
+// GPC sums in group order.  Fixed order, so still deterministic; no atomics on data.
+constexpr int FIX_HUB_MIN = 16;   // pieces beyond the first two from which the CTA shares the work
+
 template <int G, int NV>
 __global__ void __launch_bounds__(256) balanced_fixup_kernel(const BalArgs a, int apply_seg_scale) {
-    const int gl = threadIdx.x % G;
-    const long long groups = (long long)gridDim.x * (blockDim.x / G);
+    constexpr int GPC = 256 / G;                        // lane groups per CTA
+    __shared__ int hub_n;
+    __shared__ int hub_seg[GPC];
+    __shared__ long long hub_first[GPC];                // first block of the hub; bit 0: its piece is `whole`
+    __shared__ float4 hub_part[GPC][G * NV];
+    const int gl = threadIdx.x % G, g = threadIdx.x / G;
     const long long nblk = (a.nnz + CB - 1) / CB;
     const int r = a.r4 * 4;
-    for (long long b = (long long)blockIdx.x * (blockDim.x / G) + threadIdx.x / G; b < nblk; b += groups) {
-        const long long e_begin = b * CB;
-        const long long e_end = e_begin + CB < a.nnz ? e_begin + CB : a.nnz;
-        if (e_end >= a.nnz) continue;                           // last block: nothing runs on
-        // the four boundary ids are independent loads: issue them together (this kernel is a chain of
-        // global-memory latencies, nothing else)
-        const int s = __ldg(a.seg_of + e_end - 1);
-        const int s_next = __ldg(a.seg_of + e_end);
-        const int s_first = __ldg(a.seg_of + e_begin);
-        const int s_prev = e_begin > 0 ? __ldg(a.seg_of + e_begin - 1) : -1;
-        const long long nb2 = e_end + CB;                        // first entry of the block after next
-        const int s_next2 = nb2 < a.nnz ? __ldg(a.seg_of + nb2) : -1;
-        if (s_next != s) continue;                              // last segment ends with the block
-        const bool whole = s_first == s;                        // the piece starts at the block start
-        if (whole && s_prev == s) continue;                     // not the first piece
-        float4 acc[NV];
-        // first two pieces (the common case: a segment cut once) loaded together
-        float4 t0[NV], t1[NV];
-        const long long slot0 = 2 * b + (whole ? 0 : 1), slot1 = 2 * (b + 1);
-#pragma unroll
-        for (int v = 0; v < NV; ++v) {
-            const int q = gl + v * G;
-            t0[v] = t1[v] = make_float4(0, 0, 0, 0);
-            if (q < a.r4) {
-                t0[v] = *reinterpret_cast<const float4*>(a.partial + (size_t)slot0 * r + 4 * q);
-                t1[v] = *reinterpret_cast<const float4*>(a.partial + (size_t)slot1 * r + 4 * q);
-            }
-        }
-#pragma unroll
-        for (int v = 0; v < NV; ++v) {
-            acc[v] = make_float4(0, 0, 0, 0);
-            acc[v].x += t0[v].x; acc[v].y += t0[v].y; acc[v].z += t0[v].z; acc[v].w += t0[v].w;
-            acc[v].x += t1[v].x; acc[v].y += t1[v].y; acc[v].z += t1[v].z; acc[v].w += t1[v].w;
-        }
-        if (s_next2 == s) {
-            // A hub: the segment runs on over many blocks (a target node that sits in thousands of
-            // candidate lists: 100+ pieces).  Its last block follows from `ptr`, so the pieces are
-            // loaded U = 32 / NV at a time — independent loads, all in flight together — and added in block
-            // order, exactly as a one-by-one walk would add them (a chain of 100+ dependent L2 round
-            // trips otherwise: 34 us per launch at the DBP15K shape, ncu).
-            constexpr int U = 32 / NV;
-            const long long b_last = ((long long)__ldg(a.ptr + s + 1) - 1) / CB;
-            for (long long bb = b + 2; bb <= b_last; bb += U) {
-                float4 t[U][NV];
-#pragma unroll
-                for (int u = 0; u < U; ++u)
-#pragma unroll
-                    for (int v = 0; v < NV; ++v) {
-                        const int q = gl + v * G;
-                        t[u][v] = (bb + u <= b_last && q < a.r4)
-                                      ? *reinterpret_cast<const float4*>(a.partial + (size_t)(2 * (bb + u)) * r + 4 * q)
-                                      : make_float4(0, 0, 0, 0);
-                    }
-#pragma unroll
-                for (int u = 0; u < U; ++u)
-#pragma unroll
-                    for (int v = 0; v < NV; ++v) {
-                        acc[v].x += t[u][v].x; acc[v].y += t[u][v].y; acc[v].z += t[u][v].z; acc[v].w += t[u][v].w;
-                    }
-            }
-        }
+    auto store = [&](int s, const float4 (&acc)[NV]) {
         const float sc = (apply_seg_scale && a.seg_scale) ? __ldg(a.seg_scale + s) : 1.f;
 #pragma unroll
         for (int v = 0; v < NV; ++v) {
@@ -394,6 +344,97 @@ __global__ void __launch_bounds__(256) balanced_fixup_kernel(const BalArgs a, in
                 if (a.accumulate) { const float4 p = *dst; o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w; }
                 *dst = o;
             }
+        }
+    };
+    auto piece = [&](long long slot, int v) {
+        const int q = gl + v * G;
+        return q < a.r4 ? *reinterpret_cast<const float4*>(a.partial + (size_t)slot * r + 4 * q)
+                        : make_float4(0, 0, 0, 0);
+    };
+    // the loop is uniform over the CTA (it synchronises): groups beyond the last block idle along
+    for (long long base = (long long)blockIdx.x * GPC; base < nblk; base += (long long)gridDim.x * GPC) {
+        if (threadIdx.x == 0) hub_n = 0;
+        __syncthreads();
+        const long long b = base + g;
+        const long long e_begin = b * CB;
+        const long long e_end = e_begin + CB < a.nnz ? e_begin + CB : a.nnz;
+        if (b < nblk && e_end < a.nnz) {                      // (last block: nothing runs on)
+            // the boundary ids are independent loads: issue them together
+            const int s = __ldg(a.seg_of + e_end - 1);
+            const int s_next = __ldg(a.seg_of + e_end);
+            const int s_first = __ldg(a.seg_of + e_begin);
+            const int s_prev = e_begin > 0 ? __ldg(a.seg_of + e_begin - 1) : -1;
+            const long long nb2 = e_end + CB;                    // first entry of the block after next
+            const int s_next2 = nb2 < a.nnz ? __ldg(a.seg_of + nb2) : -1;
+            const bool whole = s_first == s;                    // the piece starts at the block start
+            // runs on into the next block, and this is its first piece
+            if (s_next == s && !(whole && s_prev == s)) {
+                const long long b_last = s_next2 == s ? ((long long)__ldg(a.ptr + s + 1) - 1) / CB : b + 1;
+                if (b_last - (b + 1) > FIX_HUB_MIN) {
+                    if (gl == 0) {
+                        const int h = atomicAdd(&hub_n, 1);      // (list order does not matter: hubs are independent)
+                        hub_seg[h] = s;
+                        hub_first[h] = 2 * b + (whole ? 1 : 0);
+                    }
+                } else {
+                    float4 acc[NV];
+#pragma unroll
+                    for (int v = 0; v < NV; ++v) {
+                        // first two pieces (the common case: a segment cut once) loaded together
+                        const float4 t0 = piece(2 * b + (whole ? 0 : 1), v), t1 = piece(2 * (b + 1), v);
+                        acc[v] = make_float4(0, 0, 0, 0);
+                        acc[v].x += t0.x; acc[v].y += t0.y; acc[v].z += t0.z; acc[v].w += t0.w;
+                        acc[v].x += t1.x; acc[v].y += t1.y; acc[v].z += t1.z; acc[v].w += t1.w;
+                    }
+                    for (long long bb = b + 2; bb <= b_last; ++bb)
+#pragma unroll
+                        for (int v = 0; v < NV; ++v) {
+                            const float4 t = piece(2 * bb, v);
+                            acc[v].x += t.x; acc[v].y += t.y; acc[v].z += t.z; acc[v].w += t.w;
+                        }
+                    store(s, acc);
+                }
+            }
+        }
+        __syncthreads();
+        const int nh = hub_n;
+        __syncthreads();                                          // (hub_n is reset at the top of the next pass)
+        for (int h = 0; h < nh; ++h) {
+            const int s = hub_seg[h];
+            const long long bf = hub_first[h] >> 1;
+            const bool whole = hub_first[h] & 1;
+            const long long b_last = ((long long)__ldg(a.ptr + s + 1) - 1) / CB;
+            float4 sum[NV];
+#pragma unroll
+            for (int v = 0; v < NV; ++v) sum[v] = make_float4(0, 0, 0, 0);
+            for (long long bb = bf + 2 + g; bb <= b_last; bb += 2 * GPC) {     // two independent loads per pass
+#pragma unroll
+                for (int v = 0; v < NV; ++v) {
+                    const float4 t = piece(2 * bb, v);
+                    const float4 u = bb + GPC <= b_last ? piece(2 * (bb + GPC), v) : make_float4(0, 0, 0, 0);
+                    sum[v].x += t.x; sum[v].y += t.y; sum[v].z += t.z; sum[v].w += t.w;
+                    sum[v].x += u.x; sum[v].y += u.y; sum[v].z += u.z; sum[v].w += u.w;
+                }
+            }
+#pragma unroll
+            for (int v = 0; v < NV; ++v) hub_part[g][gl + v * G] = sum[v];
+            __syncthreads();
+            if (g == 0) {
+                float4 acc[NV];
+#pragma unroll
+                for (int v = 0; v < NV; ++v) {
+                    const float4 t0 = piece(2 * bf + (whole ? 0 : 1), v), t1 = piece(2 * (bf + 1), v);
+                    acc[v] = make_float4(0, 0, 0, 0);
+                    acc[v].x += t0.x; acc[v].y += t0.y; acc[v].z += t0.z; acc[v].w += t0.w;
+                    acc[v].x += t1.x; acc[v].y += t1.y; acc[v].z += t1.z; acc[v].w += t1.w;
+                    for (int gg = 0; gg < GPC; ++gg) {
+                        const float4 t = hub_part[gg][gl + v * G];
+                        acc[v].x += t.x; acc[v].y += t.y; acc[v].z += t.z; acc[v].w += t.w;
+                    }
+                }
+                store(s, acc);
+            }
+            __syncthreads();
         }
     }
 }
