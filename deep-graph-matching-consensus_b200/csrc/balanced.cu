@@ -31,6 +31,9 @@ struct BalArgs {
     const float* g; const float* ps; const float* pt; const int* perm; const float* w2; int k;
     // output
     float* out; long long ldo; int r4; int accumulate; float* partial;
+    // ReLU backward fused into the store (dgmc_segment_gather_balanced_relu): rows of `mask` have the
+    // pitch of `out`; a finished output element is zeroed where mask <= 0
+    const float* mask;
 };
 
 // 5 CTAs per SM for NV = 1 (48 registers, 8-48 bytes of spills): 740 resident CTAs hold the whole
@@ -206,7 +209,7 @@ __device__ __noinline__ void lean_zero_rows(float* outq, long long ldo, long lon
         *reinterpret_cast<float4*>(outq + s * ldo) = make_float4(0, 0, 0, 0);
 }
 
-template <int G, bool ACC, bool SCALE>
+template <int G, bool ACC, bool SCALE, bool MASK = false>
 __global__ void __launch_bounds__(256, 5) balanced_lean_kernel(const BalArgs a) {
     constexpr int PER = CB / G;
     constexpr int BR = 4;
@@ -219,6 +222,7 @@ __global__ void __launch_bounds__(256, 5) balanced_lean_kernel(const BalArgs a) 
     const float* __restrict__ xq = a.x + 4 * gl;
     float* __restrict__ outq = a.out + 4 * gl;
     float* __restrict__ partq = a.partial + 4 * gl;
+    const float* __restrict__ maskq = MASK ? a.mask + 4 * gl : nullptr;
     const int src_div = a.src_div;
     const long long ldx = a.ldx, ldo = a.ldo;
 
@@ -301,6 +305,11 @@ __global__ void __launch_bounds__(256, 5) balanced_lean_kernel(const BalArgs a) 
                     if (live) {
                         float4* dst = reinterpret_cast<float4*>((to_partial ? partq : outq) + (act[u] & 0x7ffffffc));
                         if (ACC && !to_partial) { const float4 q = *dst; o.x += q.x; o.y += q.y; o.z += q.z; o.w += q.w; }
+                        if (MASK && !to_partial) {             // ReLU backward of the layer that produced `mask`
+                            const float4 m = ldg4(maskq + (act[u] & 0x7ffffffc));
+                            o.x = m.x > 0.f ? o.x : 0.f; o.y = m.y > 0.f ? o.y : 0.f;
+                            o.z = m.z > 0.f ? o.z : 0.f; o.w = m.w > 0.f ? o.w : 0.f;
+                        }
                         *dst = o;
                     }
                     acc = make_float4(0, 0, 0, 0);
@@ -342,6 +351,11 @@ __global__ void __launch_bounds__(256) balanced_fixup_kernel(const BalArgs a, in
                 float4* dst = reinterpret_cast<float4*>(a.out + (size_t)s * a.ldo + 4 * q);
                 float4 o = make_float4(acc[v].x * sc, acc[v].y * sc, acc[v].z * sc, acc[v].w * sc);
                 if (a.accumulate) { const float4 p = *dst; o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w; }
+                if (a.mask) {
+                    const float4 m = ldg4(a.mask + (size_t)s * a.ldo + 4 * q);
+                    o.x = m.x > 0.f ? o.x : 0.f; o.y = m.y > 0.f ? o.y : 0.f;
+                    o.z = m.z > 0.f ? o.z : 0.f; o.w = m.w > 0.f ? o.w : 0.f;
+                }
                 *dst = o;
             }
         }
@@ -462,7 +476,8 @@ static int launch_balanced(const BalArgs& a, cudaStream_t stream) {
 #define LEAN(G_, ACC_, SCALE_) balanced_lean_kernel<G_, ACC_, SCALE_><<<grid, 256, 0, stream>>>(a)
 #define LEAN_G(G_)                                                                                  \
     do {                                                                                            \
-        if (a.accumulate) { if (a.seg_scale) LEAN(G_, true, true); else LEAN(G_, true, false); }    \
+        if (a.mask) balanced_lean_kernel<G_, true, false, true><<<grid, 256, 0, stream>>>(a);      \
+        else if (a.accumulate) { if (a.seg_scale) LEAN(G_, true, true); else LEAN(G_, true, false); } \
         else { if (a.seg_scale) LEAN(G_, false, true); else LEAN(G_, false, false); }               \
     } while (0)
         if (G == 8) LEAN_G(8); else if (G == 16) LEAN_G(16); else LEAN_G(32);
@@ -474,6 +489,10 @@ static int launch_balanced(const BalArgs& a, cudaStream_t stream) {
             else balanced_fixup_kernel<32, 1><<<wave_grid(nblk, 8, 8), 256, 0, stream>>>(a, 1);
         }
         return check_launch("balanced segmented reduction", nblk > 1 ? 2 : 1);
+    }
+    if (a.mask) {
+        set_error("segment_gather_balanced_relu: rows of up to 128 channels and 32-bit offsets only");
+        return DGMC_ERR_UNSUPPORTED;
     }
 #define BAL(G, NV)                                                                                  \
     do {                                                                                            \
@@ -550,4 +569,29 @@ extern "C" int dgmc_diff_mlp_bwd_targets_balanced(const float* g, const float* p
     a.g = g; a.ps = ps; a.pt = pt; a.perm = perm; a.w2 = w2; a.k = k;
     a.out = d_pt; a.ldo = r; a.r4 = r / 4; a.accumulate = 0; a.partial = (float*)workspace;
     return launch_balanced<1>(a, stream);
+}
+
+// The transposed RelConv aggregation of the backward pass with the ReLU backward of the PREVIOUS layer
+// fused into its store: out = (out + A x) * [relu_mask > 0], where out is the gradient of that layer's
+// output (already holding the contribution of the concatenation) and relu_mask is the output itself,
+// stored with the same row pitch as out.  replaces: threshold_backward after the scatter of PyG's
+// propagate backward (rel.py:27-30,84-85).  r % 4 == 0, r <= 128.
+extern "C" int dgmc_segment_gather_balanced_relu(const int32_t* ptr, const int32_t* seg_of, const int32_t* src,
+                                                 const float* w, const float* x, int64_t ldx, float* out,
+                                                 int64_t ldo, const float* relu_mask, int64_t n_seg, int64_t nnz,
+                                                 int r, void* workspace, size_t workspace_bytes,
+                                                 dgmc_stream_t stream) {
+    DGMC_REQUIRE(ptr && x && out && relu_mask && n_seg >= 0 && nnz >= 1 && ldx >= r && ldo >= r && seg_of && src,
+                 "segment_gather_balanced_relu: bad arguments");
+    if (n_seg == 0) return DGMC_OK;
+    if (int e = bal_common("segment_gather_balanced_relu", r, out, ldo, workspace, workspace_bytes, nnz)) return e;
+    if (r > 128 || ldx % 4 != 0 || ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(relu_mask)) & 15)) {
+        set_error("segment_gather_balanced_relu: r <= 128, x and relu_mask rows 16-byte aligned");
+        return DGMC_ERR_UNSUPPORTED;
+    }
+    BalArgs a{};
+    a.ptr = ptr; a.seg_of = seg_of; a.n_seg = n_seg; a.nnz = nnz;
+    a.src = src; a.src_div = 1; a.w = w; a.x = x; a.ldx = ldx;
+    a.out = out; a.ldo = ldo; a.r4 = r / 4; a.accumulate = 1; a.partial = (float*)workspace; a.mask = relu_mask;
+    return launch_balanced<0>(a, stream);
 }

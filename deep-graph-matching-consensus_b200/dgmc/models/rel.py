@@ -27,10 +27,12 @@ class RelConv(torch.nn.Module):
         for lin in (self.lin1, self.lin2, self.root):
             lin.reset_parameters()
 
-    def forward(self, x, edge_index, relu=False, out=None, passthrough=False):
+    def forward(self, x, edge_index, relu=False, out=None, passthrough=False, relu_in=None, relu_out=None):
         """relu=True additionally applies the ReLU that RelCNN puts after every conv (rel.py:84-85),
         fused into the GEMM epilogue.  out: write the result into this column block of a layer
-        buffer; passthrough: also return x as handed through the aggregation (ops._RelAggregatePass)."""
+        buffer; passthrough: also return x as handed through the aggregation (ops._RelAggregatePass).
+        relu_in / relu_out: ops.ReluOwner of the layer that produced x / of this layer's output (RelCNN
+        chains them so that a layer's ReLU backward runs inside the next layer's aggregation backward)."""
         graph = ops.GraphCSR.of(edge_index, x.size(0))
         if ops.relconv_fused_ok(x, graph.rel, self.out_channels):
             # aggregation and GEMM in one kernel (dgmc_relconv_tc)
@@ -40,12 +42,13 @@ class RelConv(torch.nn.Module):
                                          key=('relconv', id(self)), out=out)
             return (y, alias) if passthrough else y
         if passthrough:
-            stacked, alias = ops.rel_aggregate_pass(x, graph)
+            stacked, alias = ops.rel_aggregate_pass(x, graph, relu_in)
         else:
             stacked = ops.rel_aggregate(x, graph)  # [N, 3 C_in] = [x | mean_in | mean_out]
         weight = ops.region_cached(('relconv', id(self)), lambda: torch.cat(
             [self.root.weight, self.lin1.weight, self.lin2.weight], dim=1))
-        y = ops.node_linear(stacked, weight, self.root.bias, relu=relu, key=('relconv', id(self)), out=out)
+        y = ops.node_linear(stacked, weight, self.root.bias, relu=relu, key=('relconv', id(self)), out=out,
+                            relu_owner=relu_out if relu else None)
         return (y, alias) if passthrough else y
 
     def __repr__(self):
@@ -106,8 +109,16 @@ class RelCNN(torch.nn.Module):
             buf = torch.empty(x.size(0), c_in + self.num_layers * c_out, dtype=torch.float32, device=x.device)
             cur = ops.copy_into(x, buf, 0)
         parts, off = [], c_in
+        owner = None                      # ReLU owner of `cur` (the layer input is not a ReLU output)
+        fused = ops.relconv_fused_ok(cur, ops.GraphCSR.of(edge_index, cur.size(0)).rel, c_out)
         for conv in self.convs:
-            cur, alias = conv(cur, edge_index, relu=True, out=buf[:, off:off + c_out], passthrough=True)
+            # `cur` (a layer output) is consumed by the next layer's aggregation node only — through which
+            # its share of the concatenation's gradient passes as well — so that node can apply the ReLU
+            # backward of the layer that produced it
+            nxt = None if fused else ops.ReluOwner()
+            cur, alias = conv(cur, edge_index, relu=True, out=buf[:, off:off + c_out], passthrough=True,
+                              relu_in=owner, relu_out=nxt)
+            owner = nxt
             parts.append(alias)
             off += c_out
         parts.append(cur)

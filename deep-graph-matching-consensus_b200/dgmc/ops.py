@@ -637,10 +637,20 @@ def _wgrad_tc_chunked(a, b):
     return dw
 
 
+class ReluOwner(object):
+    """Who applies the backward of a layer's ReLU.  node_linear(relu=True, relu_owner=o) leaves it to the
+    consumer of its output when that consumer announces, during the forward pass, that it will zero the
+    gradient where the output is <= 0 (o.masked = True: the transposed aggregation of the next RelConv
+    does it inside its store) — one elementwise kernel less per layer and consensus step."""
+    def __init__(self):
+        self.masked = False
+
+
 class _NodeLinear(torch.autograd.Function):
     """kn = False: weight [out, in] (torch Linear); kn = True: weight [in, out] (SplineConv)."""
     @staticmethod
-    def forward(ctx, x, weight, bias, relu, group, kn, out, bias_rows):
+    def forward(ctx, x, weight, bias, relu, group, kn, out, bias_rows, relu_owner=None):
+        ctx.relu_owner = relu_owner
         k_in, n_out = (weight.size(0), weight.size(1)) if kn else (weight.size(1), weight.size(0))
         if _linear_tc_ok(x, n_out, k_in):
             y = _linear_tc(x, _split_weight(weight, kn, group, 'split_fwd'), bias, relu, n_out, k_in, out,
@@ -674,7 +684,9 @@ class _NodeLinear(torch.autograd.Function):
     def backward(ctx, g):
         if ctx.relu:
             x, weight, y = ctx.saved_tensors
-            if g.dim() == 2 and g.stride(1) == 1 and y.stride(1) == 1 and _vec_ok(g) and _vec_ok(y) \
+            if ctx.relu_owner is not None and ctx.relu_owner.masked:
+                pass                                   # the consumer of y has already zeroed g where y <= 0
+            elif g.dim() == 2 and g.stride(1) == 1 and y.stride(1) == 1 and _vec_ok(g) and _vec_ok(y) \
                     and g.dtype == torch.float32:
                 gm = torch.empty(g.size(0), g.size(1), dtype=torch.float32, device=g.device)
                 call('dgmc_relu_bwd', RowStrided(g), g.stride(0), RowStrided(y), y.stride(0), gm, gm.stride(0),
@@ -684,7 +696,9 @@ class _NodeLinear(torch.autograd.Function):
                 g = torch.ops.aten.threshold_backward(g, y, 0)
         else:
             x, weight = ctx.saved_tensors
-        g = _f32(g)
+        # (a gradient that arrives as a column block of a wider table stays where it is when the kernels
+        # below can read it with its row pitch)
+        g = _rows_f32(g) if (g.dim() == 2 and _vec_ok(g)) else _f32(g)
         kn = ctx.kn
         k_in, n_out = (weight.size(0), weight.size(1)) if kn else (weight.size(1), weight.size(0))
         k = x.size(0)
@@ -700,7 +714,7 @@ class _NodeLinear(torch.autograd.Function):
         dw, db = _weight_grad(g, x, weight, kn, ctx.has_bias, ctx.bias_rows, ctx.group,
                               getattr(ctx, 'slot', 0), ctx.needs_input_grad[1],
                               ctx.has_bias and ctx.needs_input_grad[2])
-        return dx, dw, db, None, None, None, None, None
+        return dx, dw, db, None, None, None, None, None, None
 
 
 def _weight_grad(g, x, weight, kn, has_bias, bias_rows, grp, slot, want_w, want_b):
@@ -750,10 +764,10 @@ def _weight_grad(g, x, weight, kn, has_bias, bias_rows, grp, slot, want_w, want_
     off = slot * holder.splits
     pb = None if holder.partial_b is None else holder.partial_b[off:off + holder.splits]
     if rows_bias and tc:
-        call('dgmc_wgrad_tc_partial_rows', g, g.stride(0), RowStrided(x), x.stride(0), k, m, n,
+        call('dgmc_wgrad_tc_partial_rows', RowStrided(g), g.stride(0), RowStrided(x), x.stride(0), k, m, n,
              int(bias_rows), holder.partial[off:off + holder.splits], pb, stream_ptr())
     else:
-        call(fn_partial, g, g.stride(0), RowStrided(x), x.stride(0), k, m, n,
+        call(fn_partial, RowStrided(g), g.stride(0), RowStrided(x), x.stride(0), k, m, n,
              holder.partial[off:off + holder.splits], pb, stream_ptr())
         if rows_bias:   # the FFMA kernel sums all rows: overwrite its bias partials
             pb.zero_()
@@ -772,7 +786,8 @@ def _weight_grad(g, x, weight, kn, has_bias, bias_rows, grp, slot, want_w, want_
     return dw, db
 
 
-def node_linear(x, weight, bias=None, relu=False, key=None, kn=False, out=None, bias_rows=None):
+def node_linear(x, weight, bias=None, relu=False, key=None, kn=False, out=None, bias_rows=None,
+                relu_owner=None):
     """relu?(x [nodes, in] @ W + bias) with W = weight[out, in]^T (kn=False) or weight[in, out]
     (kn=True).  Forward and input gradient run on the tensor-core kernel dgmc_linear_tc (3xTF32,
     bias and ReLU in its epilogue) whenever x meets TMA's alignment rules, else on the library GEMM;
@@ -785,7 +800,7 @@ def node_linear(x, weight, bias=None, relu=False, key=None, kn=False, out=None, 
         group = None
         if key is not None and _DEFER[0] is not None and torch.is_grad_enabled():
             group = _DEFER[0].setdefault((key, x.size(0), tuple(weight.shape)), WGradGroup())
-        return _NodeLinear.apply(x, weight, bias, relu, group, kn, out, bias_rows)
+        return _NodeLinear.apply(x, weight, bias, relu, group, kn, out, bias_rows, relu_owner)
     assert out is None and bias_rows is None, 'node_linear(out=..., bias_rows=...) are CUDA fp32 features'
     y = torch.addmm(bias, x, weight) if (kn and bias is not None) else (
         x @ weight if kn else torch.nn.functional.linear(x, weight, bias))
@@ -836,33 +851,52 @@ class _RelAggregatePass(torch.autograd.Function):
     graph, and the backward adds the two gradients inside the gather kernel (accumulate mode, in
     place in the concatenation's gradient block) instead of in a separate add kernel."""
     @staticmethod
-    def forward(ctx, x, rel):
+    def forward(ctx, x, rel, relu_owner=None):
         x = _rows_f32(x)
         c = x.size(1)
         cat = torch.empty(rel.n_out, 3 * c, dtype=torch.float32, device=x.device)
         segment_gather(x, 3 * rel.n_out, rel.f_src, ptr=rel.f_ptr, w=rel.f_w,
                        out=cat.view(3 * rel.n_out, c), seg_of=rel.f_seg)
         ctx.rel = rel
+        # x is the ReLU output of the previous layer and this node is its only consumer: its backward
+        # zeroes the gradient where x <= 0 (see ReluOwner)
+        ctx.relu_x = None
+        if relu_owner is not None and ctx.needs_input_grad[0]:
+            relu_owner.masked = True
+            ctx.relu_x = x
         return cat, x.view_as(x)
 
     @staticmethod
     def backward(ctx, g, g_pass):
         if not ctx.needs_input_grad[0]:
-            return None, None
+            return None, None, None
         rel = ctx.rel
         g = _f32(g)
         c = g.size(1) // 3
         g_pass = _rows_f32(g_pass)
         if not _vec_ok(g_pass):
             g_pass = g_pass.contiguous()
-        dx = segment_gather(g.view(3 * rel.n_out, c), rel.n_in, rel.b_src, ptr=rel.b_ptr, w=rel.b_w,
+        y = ctx.relu_x
+        g3 = g.view(3 * rel.n_out, c)
+        if y is not None and c <= 128 and y.stride(0) == g_pass.stride(0) and _vec_ok(y) \
+                and rel.n_in * g_pass.stride(0) < 2 ** 31 and rel.b_src.numel() > 0:
+            # one kernel: g_pass = (g_pass + A^T g) * [y > 0]
+            ws = _workspace(query('dgmc_balanced_workspace', rel.b_src.numel(), c), g.device)
+            call('dgmc_segment_gather_balanced_relu', rel.b_ptr, rel.b_seg, rel.b_src, rel.b_w, g3, c,
+                 RowStrided(g_pass), g_pass.stride(0), RowStrided(y), rel.n_in, rel.b_src.numel(), c, ws,
+                 ws.numel(), stream_ptr())
+            return g_pass, None, None
+        dx = segment_gather(g3, rel.n_in, rel.b_src, ptr=rel.b_ptr, w=rel.b_w,
                             seg_of=rel.b_seg, out=g_pass, accumulate=True)
-        return dx, None
+        if y is not None:                      # the promise of the forward pass, unfused
+            dx = torch.ops.aten.threshold_backward(dx, y, 0)
+        return dx, None, None
 
 
-def rel_aggregate_pass(x, graph):
-    """-> (rel_aggregate(x, graph), x); see _RelAggregatePass."""
-    return _RelAggregatePass.apply(x, graph.rel)
+def rel_aggregate_pass(x, graph, relu_owner=None):
+    """-> (rel_aggregate(x, graph), x); see _RelAggregatePass.  relu_owner: x is the output of a
+    node_linear(relu=True, relu_owner=relu_owner) that nothing else consumes."""
+    return _RelAggregatePass.apply(x, graph.rel, relu_owner)
 
 
 # RelConv layers on the fused gather + tensor-core GEMM kernel (dgmc_relconv_tc).  OFF by default: it is

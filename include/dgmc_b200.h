@@ -132,6 +132,16 @@ int dgmc_segment_gather_balanced(const int32_t* ptr, const int32_t* seg_of, cons
                                  int64_t ldx, float* out, int64_t ldo, int64_t n_seg, int64_t nnz, int r,
                                  int accumulate, void* workspace, size_t workspace_bytes,
                                  dgmc_stream_t stream);
+/* dgmc_segment_gather_balanced in accumulate mode with a ReLU backward fused into the store:
+ *   out[s] = (out[s] + sum_{e in seg(s)} (w ? w[e] : 1) * X[src[e]]) * [relu_mask[s] > 0]   (element-wise)
+ * relu_mask rows have the pitch of out (ldo).  Every segment must have at least one entry (the transposed
+ * RelConv operator has: each node's own row).  r % 4 == 0, r <= 128, 16-byte aligned rows.
+ * replaces: the scatter of PyG's propagate backward (rel.py:27-30) followed by the threshold_backward of
+ * the ReLU after the previous conv (rel.py:84-85). */
+int dgmc_segment_gather_balanced_relu(const int32_t* ptr, const int32_t* seg_of, const int32_t* src,
+                                      const float* w, const float* x, int64_t ldx, float* out, int64_t ldo,
+                                      const float* relu_mask, int64_t n_seg, int64_t nnz, int r,
+                                      void* workspace, size_t workspace_bytes, dgmc_stream_t stream);
 int dgmc_diff_mlp_bwd_targets_balanced(const float* g, const float* ps, const float* pt,
                                        const int32_t* tptr, const int32_t* seg_of,
                                        const int32_t* perm, const float* w2, float* d_pt, int64_t n_t,
