@@ -331,15 +331,17 @@ __global__ void __launch_bounds__(256, 5) balanced_lean_kernel(const BalArgs a) 
 // but handed to the whole CTA: group g adds the pieces g, g + GPC, ... and the first group adds the
 // GPC sums in group order.  Fixed order, so still deterministic; no atomics on data.
 constexpr int FIX_HUB_MIN = 16;   // pieces beyond the first two from which the CTA shares the work
+constexpr int FIX_HUB_CAP = 64;   // hubs a CTA can put aside (further ones are walked by their group)
 
 template <int G, int NV>
 __global__ void __launch_bounds__(256) balanced_fixup_kernel(const BalArgs a, int apply_seg_scale) {
     constexpr int GPC = 256 / G;                        // lane groups per CTA
     __shared__ int hub_n;
-    __shared__ int hub_seg[GPC];
-    __shared__ long long hub_first[GPC];                // first block of the hub; bit 0: its piece is `whole`
+    __shared__ int hub_seg[FIX_HUB_CAP];
+    __shared__ long long hub_first[FIX_HUB_CAP];        // 2 * first block of the hub + (its piece is `whole`)
     __shared__ float4 hub_part[GPC][G * NV];
-    const int gl = threadIdx.x % G, g = threadIdx.x / G;
+    const int lane = threadIdx.x & 31, gl = threadIdx.x % G, g = threadIdx.x / G;
+    const unsigned gmask = G == 32 ? 0xffffffffu : (((1u << G) - 1u) << (lane - gl));
     const long long nblk = (a.nnz + CB - 1) / CB;
     const int r = a.r4 * 4;
     auto store = [&](int s, const float4 (&acc)[NV]) {
@@ -365,91 +367,119 @@ __global__ void __launch_bounds__(256) balanced_fixup_kernel(const BalArgs a, in
         return q < a.r4 ? *reinterpret_cast<const float4*>(a.partial + (size_t)slot * r + 4 * q)
                         : make_float4(0, 0, 0, 0);
     };
-    // the loop is uniform over the CTA (it synchronises): groups beyond the last block idle along
-    for (long long base = (long long)blockIdx.x * GPC; base < nblk; base += (long long)gridDim.x * GPC) {
-        if (threadIdx.x == 0) hub_n = 0;
-        __syncthreads();
-        const long long b = base + g;
+    if (threadIdx.x == 0) hub_n = 0;
+    __syncthreads();
+    // ---- pass 1: every group on its own (no barrier): segments cut into a few pieces are finished here,
+    //      hubs are put on the CTA's list ----
+    for (long long b = (long long)blockIdx.x * GPC + g; b < nblk; b += (long long)gridDim.x * GPC) {
         const long long e_begin = b * CB;
         const long long e_end = e_begin + CB < a.nnz ? e_begin + CB : a.nnz;
-        if (b < nblk && e_end < a.nnz) {                      // (last block: nothing runs on)
-            // the boundary ids are independent loads: issue them together
-            const int s = __ldg(a.seg_of + e_end - 1);
-            const int s_next = __ldg(a.seg_of + e_end);
-            const int s_first = __ldg(a.seg_of + e_begin);
-            const int s_prev = e_begin > 0 ? __ldg(a.seg_of + e_begin - 1) : -1;
-            const long long nb2 = e_end + CB;                    // first entry of the block after next
-            const int s_next2 = nb2 < a.nnz ? __ldg(a.seg_of + nb2) : -1;
-            const bool whole = s_first == s;                    // the piece starts at the block start
-            // runs on into the next block, and this is its first piece
-            if (s_next == s && !(whole && s_prev == s)) {
-                const long long b_last = s_next2 == s ? ((long long)__ldg(a.ptr + s + 1) - 1) / CB : b + 1;
-                if (b_last - (b + 1) > FIX_HUB_MIN) {
-                    if (gl == 0) {
-                        const int h = atomicAdd(&hub_n, 1);      // (list order does not matter: hubs are independent)
-                        hub_seg[h] = s;
-                        hub_first[h] = 2 * b + (whole ? 1 : 0);
-                    }
-                } else {
-                    float4 acc[NV];
+        if (e_end >= a.nnz) continue;                           // last block: nothing runs on
+        // the boundary ids are independent loads: issue them together
+        const int s = __ldg(a.seg_of + e_end - 1);
+        const int s_next = __ldg(a.seg_of + e_end);
+        const int s_first = __ldg(a.seg_of + e_begin);
+        const int s_prev = e_begin > 0 ? __ldg(a.seg_of + e_begin - 1) : -1;
+        const long long nb2 = e_end + CB;                        // first entry of the block after next
+        const int s_next2 = nb2 < a.nnz ? __ldg(a.seg_of + nb2) : -1;
+        if (s_next != s) continue;                              // last segment ends with the block
+        const bool whole = s_first == s;                        // the piece starts at the block start
+        if (whole && s_prev == s) continue;                     // not the first piece
+        const long long b_last = s_next2 == s ? ((long long)__ldg(a.ptr + s + 1) - 1) / CB : b + 1;
+        if (b_last - (b + 1) > FIX_HUB_MIN) {
+            int h = 0;
+            if (gl == 0) h = atomicAdd(&hub_n, 1);               // (list order does not matter: hubs are independent)
+            h = __shfl_sync(gmask, h, lane - gl);
+            if (h < FIX_HUB_CAP) {
+                if (gl == 0) { hub_seg[h] = s; hub_first[h] = 2 * b + (whole ? 1 : 0); }
+                continue;
+            }
+            // list full (which hubs end up here depends on timing): this group alone, but in the SAME
+            // association as pass 2, so that the result does not depend on the path
+            float4 acc[NV];
+#pragma unroll
+            for (int v = 0; v < NV; ++v) {
+                const float4 t0 = piece(2 * b + (whole ? 0 : 1), v), t1 = piece(2 * (b + 1), v);
+                acc[v] = make_float4(0, 0, 0, 0);
+                acc[v].x += t0.x; acc[v].y += t0.y; acc[v].z += t0.z; acc[v].w += t0.w;
+                acc[v].x += t1.x; acc[v].y += t1.y; acc[v].z += t1.z; acc[v].w += t1.w;
+            }
+            for (int gg = 0; gg < GPC; ++gg) {
+                float4 sum[NV];
+#pragma unroll
+                for (int v = 0; v < NV; ++v) sum[v] = make_float4(0, 0, 0, 0);
+                for (long long bb = b + 2 + gg; bb <= b_last; bb += 2 * GPC)
 #pragma unroll
                     for (int v = 0; v < NV; ++v) {
-                        // first two pieces (the common case: a segment cut once) loaded together
-                        const float4 t0 = piece(2 * b + (whole ? 0 : 1), v), t1 = piece(2 * (b + 1), v);
-                        acc[v] = make_float4(0, 0, 0, 0);
-                        acc[v].x += t0.x; acc[v].y += t0.y; acc[v].z += t0.z; acc[v].w += t0.w;
-                        acc[v].x += t1.x; acc[v].y += t1.y; acc[v].z += t1.z; acc[v].w += t1.w;
+                        const float4 t = piece(2 * bb, v);
+                        const float4 u = bb + GPC <= b_last ? piece(2 * (bb + GPC), v) : make_float4(0, 0, 0, 0);
+                        sum[v].x += t.x; sum[v].y += t.y; sum[v].z += t.z; sum[v].w += t.w;
+                        sum[v].x += u.x; sum[v].y += u.y; sum[v].z += u.z; sum[v].w += u.w;
                     }
-                    for (long long bb = b + 2; bb <= b_last; ++bb)
 #pragma unroll
-                        for (int v = 0; v < NV; ++v) {
-                            const float4 t = piece(2 * bb, v);
-                            acc[v].x += t.x; acc[v].y += t.y; acc[v].z += t.z; acc[v].w += t.w;
-                        }
-                    store(s, acc);
+                for (int v = 0; v < NV; ++v) {
+                    acc[v].x += sum[v].x; acc[v].y += sum[v].y; acc[v].z += sum[v].z; acc[v].w += sum[v].w;
                 }
             }
+            store(s, acc);
+            continue;
+        }
+        float4 acc[NV];
+#pragma unroll
+        for (int v = 0; v < NV; ++v) {
+            // first two pieces (the common case: a segment cut once) loaded together
+            const float4 t0 = piece(2 * b + (whole ? 0 : 1), v), t1 = piece(2 * (b + 1), v);
+            acc[v] = make_float4(0, 0, 0, 0);
+            acc[v].x += t0.x; acc[v].y += t0.y; acc[v].z += t0.z; acc[v].w += t0.w;
+            acc[v].x += t1.x; acc[v].y += t1.y; acc[v].z += t1.z; acc[v].w += t1.w;
+        }
+        for (long long bb = b + 2; bb <= b_last; ++bb)
+#pragma unroll
+            for (int v = 0; v < NV; ++v) {
+                const float4 t = piece(2 * bb, v);
+                acc[v].x += t.x; acc[v].y += t.y; acc[v].z += t.z; acc[v].w += t.w;
+            }
+        store(s, acc);
+    }
+    __syncthreads();
+    // ---- pass 2: the CTA's hubs, one after the other, all groups on each ----
+    const int nh = hub_n < FIX_HUB_CAP ? hub_n : FIX_HUB_CAP;
+    for (int h = 0; h < nh; ++h) {
+        const int s = hub_seg[h];
+        const long long bf = hub_first[h] >> 1;
+        const bool whole = hub_first[h] & 1;
+        const long long b_last = ((long long)__ldg(a.ptr + s + 1) - 1) / CB;
+        float4 sum[NV];
+#pragma unroll
+        for (int v = 0; v < NV; ++v) sum[v] = make_float4(0, 0, 0, 0);
+        for (long long bb = bf + 2 + g; bb <= b_last; bb += 2 * GPC) {     // two independent loads per pass
+#pragma unroll
+            for (int v = 0; v < NV; ++v) {
+                const float4 t = piece(2 * bb, v);
+                const float4 u = bb + GPC <= b_last ? piece(2 * (bb + GPC), v) : make_float4(0, 0, 0, 0);
+                sum[v].x += t.x; sum[v].y += t.y; sum[v].z += t.z; sum[v].w += t.w;
+                sum[v].x += u.x; sum[v].y += u.y; sum[v].z += u.z; sum[v].w += u.w;
+            }
+        }
+#pragma unroll
+        for (int v = 0; v < NV; ++v) hub_part[g][gl + v * G] = sum[v];
+        __syncthreads();
+        if (g == 0) {
+            float4 acc[NV];
+#pragma unroll
+            for (int v = 0; v < NV; ++v) {
+                const float4 t0 = piece(2 * bf + (whole ? 0 : 1), v), t1 = piece(2 * (bf + 1), v);
+                acc[v] = make_float4(0, 0, 0, 0);
+                acc[v].x += t0.x; acc[v].y += t0.y; acc[v].z += t0.z; acc[v].w += t0.w;
+                acc[v].x += t1.x; acc[v].y += t1.y; acc[v].z += t1.z; acc[v].w += t1.w;
+                for (int gg = 0; gg < GPC; ++gg) {
+                    const float4 t = hub_part[gg][gl + v * G];
+                    acc[v].x += t.x; acc[v].y += t.y; acc[v].z += t.z; acc[v].w += t.w;
+                }
+            }
+            store(s, acc);
         }
         __syncthreads();
-        const int nh = hub_n;
-        __syncthreads();                                          // (hub_n is reset at the top of the next pass)
-        for (int h = 0; h < nh; ++h) {
-            const int s = hub_seg[h];
-            const long long bf = hub_first[h] >> 1;
-            const bool whole = hub_first[h] & 1;
-            const long long b_last = ((long long)__ldg(a.ptr + s + 1) - 1) / CB;
-            float4 sum[NV];
-#pragma unroll
-            for (int v = 0; v < NV; ++v) sum[v] = make_float4(0, 0, 0, 0);
-            for (long long bb = bf + 2 + g; bb <= b_last; bb += 2 * GPC) {     // two independent loads per pass
-#pragma unroll
-                for (int v = 0; v < NV; ++v) {
-                    const float4 t = piece(2 * bb, v);
-                    const float4 u = bb + GPC <= b_last ? piece(2 * (bb + GPC), v) : make_float4(0, 0, 0, 0);
-                    sum[v].x += t.x; sum[v].y += t.y; sum[v].z += t.z; sum[v].w += t.w;
-                    sum[v].x += u.x; sum[v].y += u.y; sum[v].z += u.z; sum[v].w += u.w;
-                }
-            }
-#pragma unroll
-            for (int v = 0; v < NV; ++v) hub_part[g][gl + v * G] = sum[v];
-            __syncthreads();
-            if (g == 0) {
-                float4 acc[NV];
-#pragma unroll
-                for (int v = 0; v < NV; ++v) {
-                    const float4 t0 = piece(2 * bf + (whole ? 0 : 1), v), t1 = piece(2 * (bf + 1), v);
-                    acc[v] = make_float4(0, 0, 0, 0);
-                    acc[v].x += t0.x; acc[v].y += t0.y; acc[v].z += t0.z; acc[v].w += t0.w;
-                    acc[v].x += t1.x; acc[v].y += t1.y; acc[v].z += t1.z; acc[v].w += t1.w;
-                    for (int gg = 0; gg < GPC; ++gg) {
-                        const float4 t = hub_part[gg][gl + v * G];
-                        acc[v].x += t.x; acc[v].y += t.y; acc[v].z += t.z; acc[v].w += t.w;
-                    }
-                }
-                store(s, acc);
-            }
-            __syncthreads();
-        }
     }
 }
 
