@@ -34,6 +34,7 @@ struct BalArgs {
     // ReLU backward fused into the store (dgmc_segment_gather_balanced_relu): rows of `mask` have the
     // pitch of `out`; a finished output element is zeroed where mask <= 0
     const float* mask;
+    int hub_cap;   // entries of the fix-up pass's per-CTA hub list in use (<= FIX_HUB_CAP)
 };
 
 // 5 CTAs per SM for NV = 1 (48 registers, 8-48 bytes of spills): 740 resident CTAs hold the whole
@@ -390,7 +391,7 @@ __global__ void __launch_bounds__(256) balanced_fixup_kernel(const BalArgs a, in
             int h = 0;
             if (gl == 0) h = atomicAdd(&hub_n, 1);               // (list order does not matter: hubs are independent)
             h = __shfl_sync(gmask, h, lane - gl);
-            if (h < FIX_HUB_CAP) {
+            if (h < a.hub_cap) {
                 if (gl == 0) { hub_seg[h] = s; hub_first[h] = 2 * b + (whole ? 1 : 0); }
                 continue;
             }
@@ -443,7 +444,7 @@ __global__ void __launch_bounds__(256) balanced_fixup_kernel(const BalArgs a, in
     }
     __syncthreads();
     // ---- pass 2: the CTA's hubs, one after the other, all groups on each ----
-    const int nh = hub_n < FIX_HUB_CAP ? hub_n : FIX_HUB_CAP;
+    const int nh = hub_n < a.hub_cap ? hub_n : a.hub_cap;
     for (int h = 0; h < nh; ++h) {
         const int s = hub_seg[h];
         const long long bf = hub_first[h] >> 1;
@@ -491,8 +492,12 @@ __global__ void __launch_bounds__(256) balanced_zero_kernel(const BalArgs a) {
         *reinterpret_cast<float4*>(a.out + (size_t)(t / a.r4) * a.ldo + 4 * (t % a.r4)) = make_float4(0, 0, 0, 0);
 }
 
+static int g_hub_cap = FIX_HUB_CAP;
+
 template <int MODE>
-static int launch_balanced(const BalArgs& a, cudaStream_t stream) {
+static int launch_balanced(const BalArgs& a_in, cudaStream_t stream) {
+    BalArgs a = a_in;
+    a.hub_cap = g_hub_cap;
     const long long nblk = (a.nnz + CB - 1) / CB;
     if (nblk == 0) {
         if (!a.accumulate) balanced_zero_kernel<<<wave_grid(a.n_seg * a.r4, 256, 8), 256, 0, stream>>>(a);
@@ -624,4 +629,12 @@ extern "C" int dgmc_segment_gather_balanced_relu(const int32_t* ptr, const int32
     a.src = src; a.src_div = 1; a.w = w; a.x = x; a.ldx = ldx;
     a.out = out; a.ldo = ldo; a.r4 = r / 4; a.accumulate = 1; a.partial = (float*)workspace; a.mask = relu_mask;
     return launch_balanced<0>(a, stream);
+}
+
+// Test hook: how many hubs a CTA of the fix-up pass may put on its list (0 .. 64, default 64); hubs beyond
+// that are reduced by their own lane group in the same association, so results must not depend on it.
+extern "C" int dgmc_set_fixup_hub_list(int entries) {
+    DGMC_REQUIRE(entries >= 0 && entries <= FIX_HUB_CAP, "set_fixup_hub_list: 0 .. %d entries", FIX_HUB_CAP);
+    g_hub_cap = entries;
+    return DGMC_OK;
 }

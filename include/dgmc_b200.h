@@ -132,6 +132,12 @@ int dgmc_segment_gather_balanced(const int32_t* ptr, const int32_t* seg_of, cons
                                  int64_t ldx, float* out, int64_t ldo, int64_t n_seg, int64_t nnz, int r,
                                  int accumulate, void* workspace, size_t workspace_bytes,
                                  dgmc_stream_t stream);
+/* Test hook for the balanced kernels' second pass: a segment cut into more than 18 pieces (a hub) is put
+ * on its CTA's list (64 entries) and reduced by the whole CTA; hubs that find the list full are reduced by
+ * their own lane group in the same association.  entries = 0 .. 64 sets the list size in use (default 64);
+ * results must be bit-identical for every value (tests/test_gpu_kernels.py). */
+int dgmc_set_fixup_hub_list(int entries);
+
 /* dgmc_segment_gather_balanced in accumulate mode with a ReLU backward fused into the store:
  *   out[s] = (out[s] + sum_{e in seg(s)} (w ? w[e] : 1) * X[src[e]]) * [relu_mask[s] > 0]   (element-wise)
  * relu_mask rows have the pitch of out (ldo).  Every segment must have at least one entry (the transposed

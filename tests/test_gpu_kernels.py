@@ -206,6 +206,36 @@ def test_rel_aggregate(c):
     assert torch.allclose(x.grad.double(), xr.grad, rtol=1e-5, atol=1e-5)
 
 
+@pytest.mark.parametrize('c', [64, 256])
+def test_hub_segments_reduce_identically_on_every_path(c):
+    """The second pass of the balanced gathers hands a hub (a segment cut into more than 18 pieces) to
+    its whole CTA, or — when the CTA's list is full — to the hub's own lane group, which adds in the
+    same association: with the list switched off the result must be bit-identical, and right."""
+    from dgmc import native, ops
+    g = _gen(c)
+    n, e = 3000, 60000
+    dst = (torch.rand(e, generator=g).pow(4) * n).long().clamp_(max=n - 1)      # hubs of up to ~9,000 entries
+    src = torch.randint(n, (e, ), generator=g)
+    keys = dst.to(torch.int32).to(DEV)
+    ptr, perm, seg_of = ops.csr_build(keys, n, True)
+    assert int((ptr[1:] - ptr[:-1]).max()) > 2000
+    x = _randn(g, n, c)
+    w = torch.rand(e, generator=g).to(DEV)
+    srcs = src.to(torch.int32).to(DEV)[perm.long()].contiguous()
+    ws = w[perm.long()].contiguous()
+    outs = []
+    try:
+        for cap in (64, 0, 1):
+            native.call('dgmc_set_fixup_hub_list', cap)
+            outs.append(ops.segment_gather(x, n, srcs, ptr=ptr, w=ws, seg_of=seg_of).clone())
+    finally:
+        native.call('dgmc_set_fixup_hub_list', 64)
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+    ref = torch.zeros(n, c, dtype=torch.float64, device=DEV).index_add_(
+        0, dst.to(DEV), x.double()[src.to(DEV)] * w.double().unsqueeze(1))
+    assert torch.allclose(outs[0].double(), ref, rtol=1e-5, atol=1e-3)
+
+
 @pytest.mark.parametrize('dim,cin,cout', [(2, 16, 32), (3, 16, 32), (1, 8, 8), (2, 12, 10)])
 def test_splineconv_matches_oracle(dim, cin, cout):
     from dgmc.models.spline import SplineConv
